@@ -1,0 +1,35 @@
+# Build of the product library (libacmmp_b200.so, sm_100a only) and of the test
+# infrastructure under oracle/.  `python -c "import __graft_entry__ as g; g.build()"`
+# drives the same targets.
+NVCC      ?= nvcc
+CXX       ?= g++
+CC        ?= gcc
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+# the reference's arithmetic flags (src/CMakeLists.txt:19) define its results
+NVFLAGS   := -O3 --use_fast_math -std=c++17 $(ARCH) -lineinfo -Xcompiler -fPIC
+CSRC      := acmmp_b200/csrc
+LIB       := acmmp_b200/libacmmp_b200.so
+REF       := /root/reference/src
+
+all: $(LIB) oracle
+
+$(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp -lcudart
+
+oracle: oracle/liboracle.so
+
+oracle/liboracle.so: $(wildcard oracle/*.c) $(wildcard oracle/*.h)
+	$(CC) -O2 -ffp-contract=off -fPIC -shared -o $@ $(wildcard oracle/*.c) -lm
+
+# The reference's own kernels, compiled from where they lie (never copied into the
+# repo), sm_100 + the reference's flags; only built where /root/reference exists.
+ref: oracle/_ref/libacmmp_ref.so
+oracle/_ref/libacmmp_ref.so: oracle/ref_harness.cu $(wildcard oracle/ref_stub/opencv2/*.hpp)
+	@if [ -d $(REF) ]; then mkdir -p oracle/_ref && \
+	$(NVCC) -O3 --use_fast_math --maxrregcount=128 -std=c++14 -gencode arch=compute_100,code=sm_100 \
+	  -Ioracle/ref_stub -I$(REF) -Iinclude -Xcompiler -fPIC -shared -o $@ oracle/ref_harness.cu -lcudart ; \
+	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
+
+clean:
+	rm -f $(LIB) oracle/liboracle.so oracle/_ref/libacmmp_ref.so
+.PHONY: all oracle ref clean

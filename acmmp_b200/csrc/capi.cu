@@ -1,0 +1,415 @@
+// capi.cu - the C ABI of include/acmmp_b200.h: context, uploads, run sequence.
+//
+// Host-side counterpart of the reference's class ACMMP (ACMMP.cpp:107-152,
+// 447-866) and ACMMP::RunPatchMatch (ACMMP.cu:1378-1456), restructured as a
+// reusable context: buffers, textures and the stream live across problems (the
+// reference builds and tears down everything per view per stage,
+// acmmp_definitions.cpp:260-269), no cudaDeviceSynchronize between kernels
+// (stream order suffices), nothing exits the process.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/acmmp_b200.h"
+#include "kernels.h"
+#include "prior.h"
+
+using namespace acmmp;
+
+namespace {
+
+thread_local std::string g_global_error;
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct ViewImage {
+    cudaArray_t arr = nullptr;
+    cudaTextureObject_t tex = 0;
+    int w = 0, h = 0;
+};
+
+}  // namespace
+
+struct acmmp_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    std::string error;
+    acmmp_params params;
+    int compat = ACMMP_COMPAT_REF_SM100;
+    int n = 0;   // images in the problem
+    int W = 0, H = 0;
+    std::vector<acmmp_camera> cams;
+    std::vector<ViewImage> views;
+    std::vector<DevBuf> depth_maps;   // per slot
+    std::vector<int> depth_set;
+    DevBuf ref_image, d_cams, d_tex, d_depth_ptrs, d_rc, d_pairs;
+    DevBuf planes, costs, pre_costs, sel, rng, planes_snap, costs_snap;
+    DevBuf seeded, prior_planes, plane_masks, scaled_planes, tmp_a, tmp_b, tmp_c;
+    bool have_seeded = false, have_prior = false, have_scaled = false, have_warm = false;
+    bool pairs_dirty = true;
+    bool tail_done = false;
+    uint64_t launches = 0;
+    float timing[4] = {0, 0, 0, 0};
+};
+
+namespace {
+
+int fail(acmmp_ctx *ctx, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->error = buf;
+    else g_global_error = buf;
+    return code;
+}
+
+#define CU(ctx, call)                                                                          \
+    do {                                                                                       \
+        cudaError_t e__ = (call);                                                              \
+        if (e__ != cudaSuccess)                                                                \
+            return fail(ctx, ACMMP_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), \
+                        __FILE__, __LINE__);                                                   \
+    } while (0)
+
+int bind_device(acmmp_ctx *ctx) {
+    CU(ctx, cudaSetDevice(ctx->device));
+    return 0;
+}
+
+void destroy_view(ViewImage &v) {
+    if (v.tex) cudaDestroyTextureObject(v.tex);
+    if (v.arr) cudaFreeArray(v.arr);
+    v = ViewImage();
+}
+
+// cudaArray + texture object with the reference's descriptor (ACMMP.cpp:646-663):
+// float, linear filter, unnormalised coordinates, "wrap" (not honoured for
+// unnormalised coordinates: the hardware clamps).
+int make_view(acmmp_ctx *ctx, ViewImage &v, const float *img, int w, int h, bool on_device) {
+    if (v.w != w || v.h != h || !v.arr) {
+        destroy_view(v);
+        cudaChannelFormatDesc desc = cudaCreateChannelDesc(32, 0, 0, 0, cudaChannelFormatKindFloat);
+        CU(ctx, cudaMallocArray(&v.arr, &desc, w, h));
+        cudaResourceDesc res;
+        memset(&res, 0, sizeof res);
+        res.resType = cudaResourceTypeArray;
+        res.res.array.array = v.arr;
+        cudaTextureDesc td;
+        memset(&td, 0, sizeof td);
+        td.addressMode[0] = cudaAddressModeWrap;
+        td.addressMode[1] = cudaAddressModeWrap;
+        td.filterMode = cudaFilterModeLinear;
+        td.readMode = cudaReadModeElementType;
+        td.normalizedCoords = 0;
+        CU(ctx, cudaCreateTextureObject(&v.tex, &res, &td, nullptr));
+        v.w = w;
+        v.h = h;
+    }
+    CU(ctx, cudaMemcpy2DToArrayAsync(v.arr, 0, 0, img, (size_t)w * sizeof(float), (size_t)w * sizeof(float), h,
+                                     on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
+    return 0;
+}
+
+int init_mode(const acmmp_params &p) {
+    if (!p.geom_consistency && !p.hierarchy && !p.seeded) return 0;
+    if (p.seeded) return 1;
+    if (p.planar_prior) return 2;
+    if (p.upsample) return 3;
+    return 4;
+}
+
+int refresh_pairs(acmmp_ctx *ctx) {
+    if (!ctx->pairs_dirty) return 0;
+    const int n = ctx->n;
+    std::vector<cudaTextureObject_t> tex(n);
+    std::vector<const float *> dptr(n, nullptr);
+    for (int i = 0; i < n; ++i) {
+        tex[i] = ctx->views[i].tex;
+        if (i < (int)ctx->depth_maps.size() && ctx->depth_set[i]) dptr[i] = ctx->depth_maps[i].as<float>();
+    }
+    CU(ctx, ctx->d_cams.ensure(sizeof(acmmp_camera) * n));
+    CU(ctx, ctx->d_tex.ensure(sizeof(cudaTextureObject_t) * n));
+    CU(ctx, ctx->d_depth_ptrs.ensure(sizeof(float *) * n));
+    CU(ctx, ctx->d_rc.ensure(ref_const_size()));
+    CU(ctx, ctx->d_pairs.ensure(pair_const_size() * (n > 1 ? n - 1 : 1)));
+    // small synchronous copies from pageable host vectors: safe w.r.t. lifetime
+    CU(ctx, cudaMemcpyAsync(ctx->d_cams.p, ctx->cams.data(), sizeof(acmmp_camera) * n, cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaMemcpyAsync(ctx->d_tex.p, tex.data(), sizeof(cudaTextureObject_t) * n, cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaMemcpyAsync(ctx->d_depth_ptrs.p, dptr.data(), sizeof(float *) * n, cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    CU(ctx, launch_setup_pairs(ctx->d_cams.as<acmmp_camera>(), n, ctx->d_tex.as<cudaTextureObject_t>(),
+                               ctx->d_depth_ptrs.as<const float *>(), ctx->params.depth_min, ctx->params.depth_max,
+                               ctx->d_rc.as<RefConst>(), ctx->d_pairs.as<PairConst>(), ctx->stream));
+    ctx->launches++;
+    ctx->pairs_dirty = false;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *acmmp_version(void) { return "acmmp_b200 0.1 sm_100a"; }
+
+void acmmp_default_params(acmmp_params *p) {
+    if (!p) return;
+    memset(p, 0, sizeof *p);
+    p->max_iterations = 2;
+    p->patch_size = 11;
+    p->num_images = 5;
+    p->max_image_size = 3200;
+    p->radius_increment = 2;
+    p->sigma_spatial = 5.0f;
+    p->sigma_color = 3.0f;
+    p->top_k = 4;
+    p->baseline = 0.54f;
+    p->depth_min = 0.0f;
+    p->depth_max = 1.0f;
+    p->disparity_min = 0.0f;
+    p->disparity_max = 1.0f;
+}
+
+int acmmp_create(acmmp_ctx **out, int device) {
+    if (!out) return fail(nullptr, ACMMP_ERR_INVALID, "acmmp_create: null out pointer");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, ACMMP_ERR_NO_DEVICE, "no CUDA device: %s", cudaGetErrorString(e));
+    if (device < 0 || device >= count) return fail(nullptr, ACMMP_ERR_INVALID, "device %d out of range", device);
+    acmmp_ctx *ctx = new acmmp_ctx();
+    ctx->device = device;
+    acmmp_default_params(&ctx->params);
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete ctx;
+        return fail(nullptr, ACMMP_ERR_CUDA, "cannot create stream on device %d", device);
+    }
+    for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    *out = ctx;
+    return 0;
+}
+
+void acmmp_destroy(acmmp_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (auto &v : ctx->views) destroy_view(v);
+    for (auto &d : ctx->depth_maps) d.release();
+    DevBuf *bufs[] = {&ctx->ref_image, &ctx->d_cams, &ctx->d_tex, &ctx->d_depth_ptrs, &ctx->d_rc, &ctx->d_pairs,
+                      &ctx->planes, &ctx->costs, &ctx->pre_costs, &ctx->sel, &ctx->rng, &ctx->planes_snap,
+                      &ctx->costs_snap, &ctx->seeded, &ctx->prior_planes, &ctx->plane_masks, &ctx->scaled_planes,
+                      &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c};
+    for (auto *b : bufs) b->release();
+    for (auto &ev : ctx->ev)
+        if (ev) cudaEventDestroy(ev);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *acmmp_last_error(const acmmp_ctx *ctx) { return ctx ? ctx->error.c_str() : g_global_error.c_str(); }
+
+int acmmp_set_geom_consistency(acmmp_ctx *ctx, int multi_geometry) {
+    if (!ctx) return ACMMP_ERR_INVALID;
+    ctx->params.geom_consistency = 1;
+    ctx->params.max_iterations = 2;
+    if (multi_geometry) ctx->params.multi_geometry = 1;
+    return 0;
+}
+int acmmp_set_hierarchy(acmmp_ctx *ctx) {
+    if (!ctx) return ACMMP_ERR_INVALID;
+    ctx->params.hierarchy = 1;
+    return 0;
+}
+int acmmp_set_planar_prior_params(acmmp_ctx *ctx) {
+    if (!ctx) return ACMMP_ERR_INVALID;
+    ctx->params.planar_prior = 1;
+    return 0;
+}
+int acmmp_set_compat_mode(acmmp_ctx *ctx, int mode) {
+    if (!ctx) return ACMMP_ERR_INVALID;
+    if (mode != ACMMP_COMPAT_REF_SM100 && mode != ACMMP_COMPAT_UPSTREAM)
+        return fail(ctx, ACMMP_ERR_INVALID, "unknown compat mode %d", mode);
+    ctx->compat = mode;
+    return 0;
+}
+int acmmp_get_params(const acmmp_ctx *ctx, acmmp_params *out) {
+    if (!ctx || !out) return ACMMP_ERR_INVALID;
+    *out = ctx->params;
+    return 0;
+}
+int acmmp_width(const acmmp_ctx *ctx) { return ctx ? ctx->W : 0; }
+int acmmp_height(const acmmp_ctx *ctx) { return ctx ? ctx->H : 0; }
+uint64_t acmmp_launch_count(const acmmp_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int acmmp_sync(acmmp_ctx *ctx) {
+    if (!ctx) return ACMMP_ERR_INVALID;
+    if (bind_device(ctx)) return ACMMP_ERR_CUDA;
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int acmmp_set_problem(acmmp_ctx *ctx, int n, const acmmp_camera *cams, const float *const *images,
+                      int images_on_device) {
+    if (!ctx) return ACMMP_ERR_INVALID;
+    if (n < 2 || n - 1 > ACMMP_MAX_SRC_VIEWS)
+        return fail(ctx, ACMMP_ERR_INVALID, "need 1 reference + 1..%d source views, got n=%d", ACMMP_MAX_SRC_VIEWS, n);
+    if (!cams || !images) return fail(ctx, ACMMP_ERR_INVALID, "null cameras/images");
+    for (int i = 0; i < n; ++i)
+        if (cams[i].width <= 0 || cams[i].height <= 0 || !images[i])
+            return fail(ctx, ACMMP_ERR_INVALID, "view %d: bad size %dx%d or null image", i, cams[i].width, cams[i].height);
+    if (bind_device(ctx)) return ACMMP_ERR_CUDA;
+    ctx->n = n;
+    ctx->cams.assign(cams, cams + n);
+    if ((int)ctx->views.size() < n) ctx->views.resize(n);
+    for (int i = 0; i < n; ++i) {
+        int rcode = make_view(ctx, ctx->views[i], images[i], cams[i].width, cams[i].height, images_on_device != 0);
+        if (rcode) return rcode;
+    }
+    ctx->W = cams[0].width;
+    ctx->H = cams[0].height;
+    const size_t P = (size_t)ctx->W * ctx->H;
+    CU(ctx, ctx->ref_image.ensure(P * sizeof(float)));
+    CU(ctx, cudaMemcpyAsync(ctx->ref_image.p, images[0], P * sizeof(float),
+                            images_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, ctx->planes.ensure(P * sizeof(float4)));
+    CU(ctx, ctx->planes_snap.ensure(P * sizeof(float4)));
+    CU(ctx, ctx->costs.ensure(P * sizeof(float)));
+    CU(ctx, ctx->costs_snap.ensure(P * sizeof(float)));
+    CU(ctx, ctx->pre_costs.ensure(P * sizeof(float)));
+    CU(ctx, ctx->sel.ensure(P * sizeof(uint32_t)));
+    CU(ctx, ctx->rng.ensure(P * 6 * sizeof(uint32_t)));
+    // depth range widening + disparity range (ACMMP.cpp:600-606)
+    ctx->params.depth_min = cams[0].depth_min * 0.6f;
+    ctx->params.depth_max = cams[0].depth_max * 1.2f;
+    ctx->params.num_images = n;
+    ctx->params.disparity_min = cams[0].K[0] * ctx->params.baseline / ctx->params.depth_max;
+    ctx->params.disparity_max = cams[0].K[0] * ctx->params.baseline / ctx->params.depth_min;
+    ctx->depth_maps.resize(n);
+    ctx->depth_set.assign(n, 0);
+    ctx->have_seeded = ctx->have_prior = ctx->have_scaled = ctx->have_warm = false;
+    ctx->params.seeded = 0;
+    ctx->pairs_dirty = true;
+    ctx->tail_done = false;
+    // host images may be freed by the caller right after this returns
+    if (!images_on_device) CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int acmmp_set_depth_map(acmmp_ctx *ctx, int slot, const float *depth, int w, int h, int on_device) {
+    if (!ctx || !depth) return ACMMP_ERR_INVALID;
+    if (slot < 0 || slot >= ctx->n) return fail(ctx, ACMMP_ERR_INVALID, "depth slot %d out of range", slot);
+    if (w != ctx->cams[slot].width || h != ctx->cams[slot].height)
+        return fail(ctx, ACMMP_ERR_INVALID, "depth map %dx%d does not match view %d (%dx%d)", w, h, slot,
+                    ctx->cams[slot].width, ctx->cams[slot].height);
+    if (bind_device(ctx)) return ACMMP_ERR_CUDA;
+    const size_t bytes = (size_t)w * h * sizeof(float);
+    CU(ctx, ctx->depth_maps[slot].ensure(bytes));
+    CU(ctx, cudaMemcpyAsync(ctx->depth_maps[slot].p, depth, bytes,
+                            on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
+    if (!on_device) CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->depth_set[slot] = 1;
+    ctx->pairs_dirty = true;
+    return 0;
+}
+
+int acmmp_set_warm_start(acmmp_ctx *ctx, const float *depth, const float *normal3, const float *cost) {
+    if (!ctx || !depth || !normal3 || !cost) return ACMMP_ERR_INVALID;
+    if (!ctx->W) return fail(ctx, ACMMP_ERR_STATE, "acmmp_set_problem first");
+    if (bind_device(ctx)) return ACMMP_ERR_CUDA;
+    const size_t P = (size_t)ctx->W * ctx->H;
+    CU(ctx, ctx->tmp_a.ensure(P * 3 * sizeof(float)));
+    CU(ctx, ctx->tmp_b.ensure(P * sizeof(float)));
+    CU(ctx, cudaMemcpyAsync(ctx->tmp_a.p, normal3, P * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaMemcpyAsync(ctx->tmp_b.p, depth, P * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaMemcpyAsync(ctx->costs.p, cost, P * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, launch_pack_planes(ctx->planes.as<float4>(), (int)P, ctx->tmp_a.as<float>(), ctx->tmp_b.as<float>(), 0, ctx->stream));
+    ctx->launches++;
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->have_warm = true;
+    return 0;
+}
+
+int acmmp_set_hierarchy_inputs(acmmp_ctx *ctx, const float *coarse_normal3, const float *coarse_cost, int cw, int ch,
+                               const float *fine_depth) {
+    if (!ctx || !coarse_normal3 || !coarse_cost || !fine_depth) return ACMMP_ERR_INVALID;
+    if (!ctx->W) return fail(ctx, ACMMP_ERR_STATE, "acmmp_set_problem first");
+    if (cw <= 0 || ch <= 0) return fail(ctx, ACMMP_ERR_INVALID, "bad coarse size %dx%d", cw, ch);
+    if (bind_device(ctx)) return ACMMP_ERR_CUDA;
+    const size_t P = (size_t)ctx->W * ctx->H, CP = (size_t)cw * ch;
+    CU(ctx, ctx->tmp_a.ensure(CP * 3 * sizeof(float)));
+    CU(ctx, ctx->tmp_b.ensure(CP * sizeof(float)));
+    CU(ctx, ctx->tmp_c.ensure(P * sizeof(float)));
+    CU(ctx, ctx->scaled_planes.ensure(CP * sizeof(float4)));
+    CU(ctx, cudaMemcpyAsync(ctx->tmp_a.p, coarse_normal3, CP * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaMemcpyAsync(ctx->tmp_b.p, coarse_cost, CP * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaMemcpyAsync(ctx->tmp_c.p, fine_depth, P * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    // coarse (world normal, COST in .w): ACMMP.cpp:777-792 with upsample = true.
+    // The reference decides `upsample` by comparing the coarse width with the image
+    // ROWS (ACMMP.cpp:766), i.e. it is true unless cw == H && ch == W.
+    ctx->params.upsample = (cw != ctx->H || ch != ctx->W) ? 1 : 0;
+    ctx->params.scaled_cols = (float)cw;
+    ctx->params.scaled_rows = (float)ch;
+    CU(ctx, launch_pack_planes(ctx->scaled_planes.as<float4>(), (int)CP, ctx->tmp_a.as<float>(), ctx->tmp_b.as<float>(), 0, ctx->stream));
+    // fine planes: only .w (JBU depth) is defined by the reference (ACMMP.cpp:797-804
+    // leaves x,y,z uninitialised); zeros are the defined stand-in.
+    CU(ctx, launch_pack_planes(ctx->planes.as<float4>(), (int)P, nullptr, ctx->tmp_c.as<float>(), 1, ctx->stream));
+    ctx->launches += 2;
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->have_scaled = true;
+    return 0;
+}
+
+int acmmp_set_seeded_planes(acmmp_ctx *ctx, const float *planes4) {
+    if (!ctx || !planes4) return ACMMP_ERR_INVALID;
+    if (!ctx->W) return fail(ctx, ACMMP_ERR_STATE, "acmmp_set_problem first");
+    if (bind_device(ctx)) return ACMMP_ERR_CUDA;
+    const size_t P = (size_t)ctx->W * ctx->H;
+    CU(ctx, ctx->seeded.ensure(P * sizeof(float4)));
+    CU(ctx, cudaMemcpyAsync(ctx->seeded.p, planes4, P * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->have_seeded = true;
+    ctx->params.seeded = 1;
+    return 0;
+}
+
+int acmmp_set_planar_prior(acmmp_ctx *ctx, const float *planes4, const uint32_t *mask) {
+    if (!ctx || !planes4 || !mask) return ACMMP_ERR_INVALID;
+    if (!ctx->W) return fail(ctx, ACMMP_ERR_STATE, "acmmp_set_problem first");
+    if (bind_device(ctx)) return ACMMP_ERR_CUDA;
+    const size_t P = (size_t)ctx->W * ctx->H;
+    CU(ctx, ctx->prior_planes.ensure(P * sizeof(float4)));
+    CU(ctx, ctx->plane_masks.ensure(P * sizeof(uint32_t)));
+    CU(ctx, cudaMemcpyAsync(ctx->prior_planes.p, planes4, P * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaMemcpyAsync(ctx->plane_masks.p, mask, P * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->have_prior = true;
+    return 0;
+}
+
+}  // extern "C"
+
+#include "capi_run.cu.inc"

@@ -1,0 +1,67 @@
+// kernels.h - host-visible launch interface of kernels.cu (internal, C++).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/acmmp_b200.h"
+
+namespace acmmp {
+
+struct PairConst;
+struct RefConst;
+
+struct InitLaunch {
+    float4 *planes;
+    float *costs;
+    float *pre_costs;
+    uint32_t *selected_views;
+    const float4 *seeded_planes;
+    const float4 *prior_planes;
+    const uint32_t *plane_masks;
+    const float4 *scaled_planes;
+    uint32_t *rng6;
+    const float *ref_image;
+    const PairConst *pairs;
+    const RefConst *rc;
+    int W, H, nsrc, mode, hierarchy, top_k;
+    float sigma_spatial, sigma_color, scaled_cols, scaled_rows;
+};
+
+struct SweepLaunch {
+    const float4 *planes_in;
+    const float *costs_in;
+    float4 *planes;
+    float *costs;
+    uint32_t *selected_views;
+    const float *pre_costs;
+    const float4 *prior_planes;
+    const uint32_t *plane_masks;
+    uint32_t *rng6;
+    const float *ref_image;
+    const PairConst *pairs;
+    const RefConst *rc;
+    int W, H, nsrc, iter, color;
+    float sigma_spatial, sigma_color;
+    int geom_consistency, planar_prior, hierarchy, compat;
+};
+
+cudaError_t launch_setup_pairs(const acmmp_camera *d_cams, int n, const cudaTextureObject_t *d_tex,
+                               const float *const *d_depth_maps, float depth_min, float depth_max,
+                               RefConst *d_rc, PairConst *d_pairs, cudaStream_t st);
+cudaError_t launch_rng_init(unsigned long long seed, int W, int H, uint32_t *d_rng6, cudaStream_t st);
+cudaError_t launch_init(const InitLaunch &L, cudaStream_t st);
+cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st);
+cudaError_t launch_depth_normal(float4 *planes, const RefConst *rc, int W, int H, cudaStream_t st);
+cudaError_t launch_median_filter(float4 *planes, const float *costs, int W, int H, int color, cudaStream_t st);
+cudaError_t launch_split_maps(const float4 *planes, int n, float *depth, float *normal3, cudaStream_t st);
+cudaError_t launch_pack_planes(float4 *planes, int n, const float *normal3, const float *w, int zero_normal,
+                               cudaStream_t st);
+cudaError_t launch_jbu_depth(const float *image, int w, int h, const float *sdepth, int sw, int sh, int scale,
+                             float *out, cudaStream_t st);
+cudaError_t launch_resize_linear(const float *src, int sw, int sh, float *dst, int dw, int dh, cudaStream_t st);
+cudaError_t launch_fp32_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
+cudaError_t launch_mufu_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
+size_t pair_const_size();
+size_t ref_const_size();
+
+}  // namespace acmmp

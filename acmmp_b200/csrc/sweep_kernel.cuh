@@ -1,0 +1,93 @@
+// sweep_kernel.cuh - one red or black half-sweep of adaptive-checkerboard
+// propagation + multi-hypothesis joint view selection + plane refinement.
+//
+// What it computes is the reference's CheckerboardPropagation +
+// PlaneHypothesisRefinement (ACMMP.cu:707-1173) for every pixel of one colour.
+// How it is organised is new:
+//
+//  * 8 lanes per pixel ("group"), 4 pixels per warp, 32 pixels per 256-thread
+//    CTA.  Lane j owns neighbour arm j (0 up_near, 1 up_far, 2 down_near,
+//    3 down_far, 4 left_near, 5 left_far, 6 right_near, 7 right_far): it scans
+//    its candidate strip, fetches the winning plane and scores it against all
+//    sources.  The 8 x (N-1) cost matrix lives in shared memory (the reference
+//    keeps it, plus six more 32-float arrays, in 1,888 B of per-thread local
+//    memory).  Votes, the multinomial view sampling and the arg-min / arg-max
+//    run on shuffles inside the group.
+//  * the hypothesis-independent half of every NCC (36 bilateral weights and
+//    the reference-patch moments) is computed once per pixel per launch
+//    (RefPatch, ncc.cuh); camera-pair constants once per problem (PairConst).
+//  * the current plane and the 5 refinement candidates are only scored against
+//    the views that were actually sampled (view weight > 0) - the reference
+//    scores all N-1 and multiplies the rest by zero - and those (candidate,
+//    view) tasks are spread over the 8 lanes.
+//  * the XORWOW state stays in registers for the whole sweep (every lane of a
+//    group carries an identical copy, so all lanes make the same draws).
+//  * same-colour reads (the V-shaped near-arm candidates sit on the colour
+//    being rewritten, a data race in the reference) come from a snapshot of
+//    planes/costs taken before the launch: deterministic, and what the
+//    reference does whenever the neighbour has not finished yet.
+#pragma once
+#include "common.cuh"
+#include "geometry.cuh"
+#include "ncc.cuh"
+
+namespace acmmp {
+
+constexpr int kGroup = 8;                 // lanes per pixel
+constexpr int kGroupsPerCta = 32;         // pixels per CTA
+constexpr int kSweepThreads = kGroup * kGroupsPerCta;
+constexpr int kTileW = 16, kTileH = 4;    // 64 pixels, 32 of each colour
+
+struct SweepArgs {
+    // snapshot (read) and live (write) state
+    const float4 *planes_in;
+    const float *costs_in;
+    float4 *planes;
+    float *costs;
+    uint32_t *selected_views;
+    const float *pre_costs;
+    const float4 *prior_planes;
+    const uint32_t *plane_masks;
+    RngPlanes rng;
+    const float *ref_image;   // row-major reference image
+    const PairConst *pairs;   // nsrc
+    const RefConst *rc;
+    int nsrc;
+    int iter;
+    int color;                // 0 black ((x+y) even), 1 red
+    float sigma_spatial, sigma_color;
+    int geom_consistency, planar_prior, hierarchy;
+    int compat;               // acmmp_compat_mode
+};
+
+// Per-pixel shared-memory block.  nsrc-sized arrays follow the fixed part.
+struct GroupSmemFixed {
+    RefPatch rp;
+};
+
+ACMMP_DEV size_t group_smem_floats(int nsrc) {
+    // cm[nsrc][8] + task costs [6][nsrc] + probs[nsrc]
+    return (size_t)nsrc * 8 + (size_t)6 * nsrc + nsrc;
+}
+
+__host__ __device__ inline size_t sweep_smem_bytes(int nsrc) {
+    size_t per_group = sizeof(GroupSmemFixed) + ((size_t)nsrc * 8 + (size_t)6 * nsrc + nsrc) * sizeof(float);
+    per_group = (per_group + 15) & ~(size_t)15;
+    size_t pairs = ((size_t)nsrc * sizeof(PairConst) + 15) & ~(size_t)15;
+    size_t rc = (sizeof(RefConst) + 15) & ~(size_t)15;
+    return pairs + rc + per_group * kGroupsPerCta;
+}
+
+// group-scoped shuffle helpers
+struct Grp {
+    unsigned mask;   // lanes of this group inside the warp
+    int base;        // first lane of the group
+    int lane;        // 0..7
+    ACMMP_DEV float shfl(float v, int src) const { return __shfl_sync(mask, v, base + src); }
+    ACMMP_DEV int shfl(int v, int src) const { return __shfl_sync(mask, v, base + src); }
+    ACMMP_DEV unsigned shfl(unsigned v, int src) const { return __shfl_sync(mask, v, base + src); }
+    ACMMP_DEV void sync() const { __syncwarp(mask); }
+    ACMMP_DEV unsigned ballot(bool p) const { return (__ballot_sync(mask, p) >> base) & 0xffu; }
+};
+
+}  // namespace acmmp

@@ -1,0 +1,224 @@
+"""Python host-side mirror of the reference's operator interface for the hot path:
+`class ACMMP` (ACMMP.h:58-90) and `RunJBU` (ACMMP.h:18-20), calling the CUDA
+library through the C ABI.  Method names, call order and argument meaning follow
+the reference; cv::Mat becomes numpy, file names become in-memory arrays (the
+file-based driver lives in pipeline.py).  Host logic only - no arithmetic of the
+path is done in Python."""
+import ctypes as C
+
+import numpy as np
+
+from . import lib as L
+
+
+def _check(ctx, rc, what):
+    if rc != 0:
+        msg = L.load().acmmp_last_error(ctx).decode() if ctx else L.load().acmmp_last_error(None).decode()
+        raise L.AcmmpError(f"{what} failed ({rc}): {msg}")
+
+
+class ACMMP:
+    """One per (device); reusable across problems (the reference constructs one
+    per view per stage, acmmp_definitions.cpp:260)."""
+
+    def __init__(self, device=0):
+        self._lib = L.load()
+        self._ctx = C.c_void_p()
+        rc = self._lib.acmmp_create(C.byref(self._ctx), device)
+        if rc != 0:
+            raise L.AcmmpError(f"acmmp_create failed ({rc}): {self._lib.acmmp_last_error(None).decode()}")
+        self.device = device
+        self._flags = []
+
+    def close(self):
+        if self._ctx:
+            self._lib.acmmp_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- mode setters (ACMMP.cpp:447-464); applied at InputInitialization -------
+    def SetGeomConsistencyParams(self, multi_geometry=False):
+        _check(self._ctx, self._lib.acmmp_set_geom_consistency(self._ctx, int(multi_geometry)), "SetGeomConsistencyParams")
+
+    def SetHierarchyParams(self):
+        _check(self._ctx, self._lib.acmmp_set_hierarchy(self._ctx), "SetHierarchyParams")
+
+    def SetPlanarPriorParams(self):
+        _check(self._ctx, self._lib.acmmp_set_planar_prior_params(self._ctx), "SetPlanarPriorParams")
+
+    def SetCompatMode(self, mode):
+        _check(self._ctx, self._lib.acmmp_set_compat_mode(self._ctx, int(mode)), "SetCompatMode")
+
+    # ---- inputs ---------------------------------------------------------------------
+    def InputInitialization(self, images, cams, depths=None):
+        """images[0] / cams[0]: reference view (float32 HxW at this scale); the
+        rest are the sources.  `depths`: per-view depth maps for geometric
+        consistency (ACMMP.cpp:608-635)."""
+        n = len(images)
+        imgs = [L.f32(im) for im in images]
+        for im, cam in zip(imgs, cams):
+            if im.shape != (cam.height, cam.width):
+                raise L.AcmmpError(f"image {im.shape} does not match camera {cam.height}x{cam.width}")
+        cam_arr = (L.Camera * n)(*[c.copy() for c in cams])
+        ptrs = (C.c_void_p * n)(*[im.ctypes.data for im in imgs])
+        _check(self._ctx, self._lib.acmmp_set_problem(self._ctx, n, cam_arr, ptrs, 0), "InputInitialization")
+        if depths is not None:
+            for i, d in enumerate(depths):
+                if d is None:
+                    continue
+                d = L.f32(d)
+                _check(self._ctx, self._lib.acmmp_set_depth_map(self._ctx, i, d.ctypes.data, d.shape[1], d.shape[0], 0),
+                       "set_depth_map")
+
+    def CudaSpaceInitialization(self, warm_start=None, hierarchy=None):
+        """warm_start = (depth, normal[H,W,3], cost) of this view's previous stage
+        (ACMMP.cpp:710-742); hierarchy = (coarse_normal, coarse_cost, fine_depth)
+        (ACMMP.cpp:745-808)."""
+        if warm_start is not None:
+            d, n, c = (L.f32(a) for a in warm_start)
+            _check(self._ctx, self._lib.acmmp_set_warm_start(self._ctx, L.fptr(d), L.fptr(n), L.fptr(c)), "set_warm_start")
+        if hierarchy is not None:
+            cn, cc, fd = (L.f32(a) for a in hierarchy)
+            _check(self._ctx, self._lib.acmmp_set_hierarchy_inputs(self._ctx, L.fptr(cn), L.fptr(cc), cc.shape[1], cc.shape[0], L.fptr(fd)),
+                   "set_hierarchy_inputs")
+
+    def SetPlanarPrior(self, planes):
+        """fixed per-pixel plane hypotheses = the reference's `seeded` mode."""
+        p = L.f32(planes)
+        _check(self._ctx, self._lib.acmmp_set_seeded_planes(self._ctx, L.fptr(p)), "SetPlanarPrior")
+
+    def CudaPlanarPriorInitialization(self, planes, masks):
+        p = L.f32(planes)
+        m = np.ascontiguousarray(masks, dtype=np.uint32)
+        _check(self._ctx, self._lib.acmmp_set_planar_prior(self._ctx, L.fptr(p), L.uptr(m)), "CudaPlanarPriorInitialization")
+
+    def BuildPlanarPrior(self):
+        """GetSupportPoints -> DelaunayTriangulation -> raster -> plane fit -> upload."""
+        ns, nt = C.c_int(), C.c_int()
+        _check(self._ctx, self._lib.acmmp_build_planar_prior(self._ctx, C.byref(ns), C.byref(nt)), "BuildPlanarPrior")
+        return ns.value, nt.value
+
+    # ---- run ----------------------------------------------------------------------------
+    def RunPatchMatch(self, seed=0):
+        _check(self._ctx, self._lib.acmmp_run(self._ctx, int(seed)), "RunPatchMatch")
+
+    def run_init(self, seed=0):
+        _check(self._ctx, self._lib.acmmp_run_init(self._ctx, int(seed)), "run_init")
+
+    def run_sweep(self, it, color):
+        _check(self._ctx, self._lib.acmmp_run_sweep(self._ctx, int(it), int(color)), "run_sweep")
+
+    def run_tail(self):
+        _check(self._ctx, self._lib.acmmp_run_tail(self._ctx), "run_tail")
+
+    def sync(self):
+        _check(self._ctx, self._lib.acmmp_sync(self._ctx), "sync")
+
+    # ---- outputs ------------------------------------------------------------------------
+    def GetReferenceImageWidth(self):
+        return self._lib.acmmp_width(self._ctx)
+
+    def GetReferenceImageHeight(self):
+        return self._lib.acmmp_height(self._ctx)
+
+    def params(self):
+        p = L.Params()
+        _check(self._ctx, self._lib.acmmp_get_params(self._ctx, C.byref(p)), "get_params")
+        return p
+
+    def GetMinDepth(self):
+        return self.params().depth_min
+
+    def GetMaxDepth(self):
+        return self.params().depth_max
+
+    def _shape(self):
+        return self.GetReferenceImageHeight(), self.GetReferenceImageWidth()
+
+    def GetPlaneHypotheses(self):
+        """(H,W,4): world normal + depth after RunPatchMatch (ACMMP.cpp:848-851)."""
+        h, w = self._shape()
+        out = np.empty((h, w, 4), np.float32)
+        _check(self._ctx, self._lib.acmmp_get_result(self._ctx, L.fptr(out), None, None), "GetPlaneHypothesis")
+        return out
+
+    def GetCosts(self):
+        h, w = self._shape()
+        out = np.empty((h, w), np.float32)
+        _check(self._ctx, self._lib.acmmp_get_result(self._ctx, None, L.fptr(out), None), "GetCost")
+        return out
+
+    def GetMaps(self):
+        """depth (H,W), normal (H,W,3), cost (H,W): the three .dmb payloads."""
+        h, w = self._shape()
+        d = np.empty((h, w), np.float32)
+        n = np.empty((h, w, 3), np.float32)
+        c = np.empty((h, w), np.float32)
+        _check(self._ctx, self._lib.acmmp_get_maps(self._ctx, L.fptr(d), L.fptr(n), L.fptr(c)), "get_maps")
+        return d, n, c
+
+    def get_state(self, with_rng=True):
+        h, w = self._shape()
+        planes = np.empty((h, w, 4), np.float32)
+        costs = np.empty((h, w), np.float32)
+        sel = np.empty((h, w), np.uint32)
+        rng = np.empty((h, w, 6), np.uint32) if with_rng else None
+        _check(self._ctx, self._lib.acmmp_get_state(self._ctx, L.fptr(planes), L.fptr(costs), L.uptr(sel), L.uptr(rng)), "get_state")
+        return planes, costs, sel, rng
+
+    def set_state(self, planes=None, costs=None, sel=None, rng=None):
+        planes = L.f32(planes) if planes is not None else None
+        costs = L.f32(costs) if costs is not None else None
+        sel = np.ascontiguousarray(sel, np.uint32) if sel is not None else None
+        rng = np.ascontiguousarray(rng, np.uint32) if rng is not None else None
+        _check(self._ctx, self._lib.acmmp_set_state(self._ctx, L.fptr(planes), L.fptr(costs), L.uptr(sel), L.uptr(rng)), "set_state")
+
+    def launch_count(self):
+        return int(self._lib.acmmp_launch_count(self._ctx))
+
+    def last_timing(self):
+        out = (C.c_float * 4)()
+        _check(self._ctx, self._lib.acmmp_last_timing(self._ctx, C.byref(out)), "last_timing")
+        return {"init_ms": out[0], "sweeps_ms": out[1], "tail_ms": out[2], "total_ms": out[3]}
+
+
+def RunJBU(image, src_depth, device=0):
+    """Joint bilateral upsample of `src_depth` to the size of `image`
+    (RunJBU, ACMMP.cpp:1022-1087).  Returns None when the integer scale is 1."""
+    lib = L.load()
+    img = L.f32(image)
+    dep = L.f32(src_depth)
+    out = np.empty_like(img)
+    rc = lib.acmmp_jbu_depth(device, L.fptr(img), img.shape[1], img.shape[0], L.fptr(dep), dep.shape[1], dep.shape[0], L.fptr(out))
+    if rc == 1:
+        return None
+    _check(None, rc, "RunJBU")
+    return out
+
+
+def resize_linear(image, new_w, new_h, device=0):
+    """cv::resize(INTER_LINEAR) of a float image on the device (ACMMP.cpp:589)."""
+    lib = L.load()
+    img = L.f32(image)
+    out = np.empty((new_h, new_w), np.float32)
+    _check(None, lib.acmmp_resize_linear(device, L.fptr(img), img.shape[1], img.shape[0], L.fptr(out), new_w, new_h), "resize_linear")
+    return out
+
+
+def rng_init_states(seed, w, h, device=0):
+    lib = L.load()
+    out = np.empty((h, w, 6), np.uint32)
+    _check(None, lib.acmmp_rng_init_states(device, int(seed), w, h, L.uptr(out)), "rng_init_states")
+    return out
+
+
+def measure_fp32_peak(device=0):
+    lib = L.load()
+    a, b = C.c_double(), C.c_double()
+    _check(None, lib.acmmp_measure_fp32_peak(device, C.byref(a), C.byref(b)), "measure_fp32_peak")
+    return a.value, b.value

@@ -1,0 +1,131 @@
+"""ctypes binding of the C ABI (include/acmmp_b200.h).  No compute happens here."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libacmmp_b200.so")
+
+MAX_SRC_VIEWS = 32
+COMPAT_REF_SM100 = 0
+COMPAT_UPSTREAM = 1
+
+
+class Camera(C.Structure):
+    """= reference `struct Camera` (acmmp_definitions.h:47-55), 100 bytes."""
+    _fields_ = [("K", C.c_float * 9), ("R", C.c_float * 9), ("t", C.c_float * 3),
+                ("height", C.c_int32), ("width", C.c_int32),
+                ("depth_min", C.c_float), ("depth_max", C.c_float)]
+
+    @staticmethod
+    def make(K, R, t, width, height, depth_min, depth_max):
+        c = Camera()
+        c.K[:] = [float(x) for x in np.asarray(K, np.float32).reshape(9)]
+        c.R[:] = [float(x) for x in np.asarray(R, np.float32).reshape(9)]
+        c.t[:] = [float(x) for x in np.asarray(t, np.float32).reshape(3)]
+        c.width, c.height = int(width), int(height)
+        c.depth_min, c.depth_max = float(depth_min), float(depth_max)
+        return c
+
+    def copy(self):
+        c = Camera()
+        C.memmove(C.byref(c), C.byref(self), C.sizeof(Camera))
+        return c
+
+
+class Params(C.Structure):
+    """= reference `struct PatchMatchParams` (ACMMP.h:32-56), flags as int32."""
+    _fields_ = [("max_iterations", C.c_int32), ("patch_size", C.c_int32), ("num_images", C.c_int32),
+                ("max_image_size", C.c_int32), ("radius_increment", C.c_int32),
+                ("sigma_spatial", C.c_float), ("sigma_color", C.c_float), ("top_k", C.c_int32),
+                ("baseline", C.c_float), ("depth_min", C.c_float), ("depth_max", C.c_float),
+                ("disparity_min", C.c_float), ("disparity_max", C.c_float),
+                ("scaled_cols", C.c_float), ("scaled_rows", C.c_float),
+                ("geom_consistency", C.c_int32), ("planar_prior", C.c_int32), ("multi_geometry", C.c_int32),
+                ("hierarchy", C.c_int32), ("upsample", C.c_int32), ("seeded", C.c_int32)]
+
+
+assert C.sizeof(Camera) == 100
+
+EXPORTS = [
+    "acmmp_create", "acmmp_destroy", "acmmp_last_error", "acmmp_version", "acmmp_default_params",
+    "acmmp_set_geom_consistency", "acmmp_set_hierarchy", "acmmp_set_planar_prior_params",
+    "acmmp_set_compat_mode", "acmmp_get_params", "acmmp_set_problem", "acmmp_set_depth_map",
+    "acmmp_set_warm_start", "acmmp_set_hierarchy_inputs", "acmmp_set_seeded_planes",
+    "acmmp_set_planar_prior", "acmmp_build_planar_prior", "acmmp_run", "acmmp_run_init",
+    "acmmp_run_sweep", "acmmp_run_tail", "acmmp_get_result", "acmmp_get_maps",
+    "acmmp_get_depth_device", "acmmp_get_state", "acmmp_set_state", "acmmp_width", "acmmp_height",
+    "acmmp_sync", "acmmp_launch_count", "acmmp_last_timing", "acmmp_jbu_depth", "acmmp_resize_linear",
+    "acmmp_rng_init_states", "acmmp_measure_fp32_peak",
+]
+
+_lib = None
+
+
+class AcmmpError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen the CUDA library; raises if it was not built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise AcmmpError(f"{LIB_PATH} not built: run `make` or __graft_entry__.build() (no CPU fallback exists)")
+    lib = C.CDLL(LIB_PATH)
+    vp, fp, up = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32)
+    lib.acmmp_create.argtypes = [C.POINTER(vp), C.c_int]
+    lib.acmmp_destroy.argtypes = [vp]
+    lib.acmmp_destroy.restype = None
+    lib.acmmp_last_error.argtypes = [vp]
+    lib.acmmp_last_error.restype = C.c_char_p
+    lib.acmmp_version.restype = C.c_char_p
+    lib.acmmp_default_params.argtypes = [C.POINTER(Params)]
+    lib.acmmp_default_params.restype = None
+    lib.acmmp_set_geom_consistency.argtypes = [vp, C.c_int]
+    lib.acmmp_set_hierarchy.argtypes = [vp]
+    lib.acmmp_set_planar_prior_params.argtypes = [vp]
+    lib.acmmp_set_compat_mode.argtypes = [vp, C.c_int]
+    lib.acmmp_get_params.argtypes = [vp, C.POINTER(Params)]
+    lib.acmmp_set_problem.argtypes = [vp, C.c_int, C.POINTER(Camera), C.POINTER(vp), C.c_int]
+    lib.acmmp_set_depth_map.argtypes = [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int]
+    lib.acmmp_set_warm_start.argtypes = [vp, fp, fp, fp]
+    lib.acmmp_set_hierarchy_inputs.argtypes = [vp, fp, fp, C.c_int, C.c_int, fp]
+    lib.acmmp_set_seeded_planes.argtypes = [vp, fp]
+    lib.acmmp_set_planar_prior.argtypes = [vp, fp, up]
+    lib.acmmp_build_planar_prior.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.acmmp_run.argtypes = [vp, C.c_uint64]
+    lib.acmmp_run_init.argtypes = [vp, C.c_uint64]
+    lib.acmmp_run_sweep.argtypes = [vp, C.c_int, C.c_int]
+    lib.acmmp_run_tail.argtypes = [vp]
+    lib.acmmp_get_result.argtypes = [vp, fp, fp, up]
+    lib.acmmp_get_maps.argtypes = [vp, fp, fp, fp]
+    lib.acmmp_get_depth_device.argtypes = [vp, C.POINTER(vp)]
+    lib.acmmp_get_state.argtypes = [vp, fp, fp, up, up]
+    lib.acmmp_set_state.argtypes = [vp, fp, fp, up, up]
+    lib.acmmp_width.argtypes = [vp]
+    lib.acmmp_height.argtypes = [vp]
+    lib.acmmp_sync.argtypes = [vp]
+    lib.acmmp_launch_count.argtypes = [vp]
+    lib.acmmp_launch_count.restype = C.c_uint64
+    lib.acmmp_last_timing.argtypes = [vp, C.POINTER(C.c_float * 4)]
+    lib.acmmp_jbu_depth.argtypes = [C.c_int, fp, C.c_int, C.c_int, fp, C.c_int, C.c_int, fp]
+    lib.acmmp_resize_linear.argtypes = [C.c_int, fp, C.c_int, C.c_int, fp, C.c_int, C.c_int]
+    lib.acmmp_rng_init_states.argtypes = [C.c_int, C.c_uint64, C.c_int, C.c_int, up]
+    lib.acmmp_measure_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    _lib = lib
+    return lib
+
+
+def fptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float)) if a is not None else None
+
+
+def uptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_uint32)) if a is not None else None
+
+
+def f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)

@@ -1,0 +1,226 @@
+/*
+ * acmmp_b200.h - C ABI of the B200-native ACMMP per-view PatchMatch hot path.
+ *
+ * This is the drop-in boundary.  The reference has no FFI; its "operator API"
+ * for this path is the C++ host class `ACMMP` (+ `JBU`/`RunJBU`) declared in
+ * /root/reference/src/ACMMP.h:58-124,142-160,18-20 and driven by
+ * ProcessProblem / JointBilateralUpsampling
+ * (/root/reference/src/acmmp_definitions.cpp:245-440).  Every entry point below
+ * names the reference member it replaces.  The C++ host class in
+ * acmmp_b200/host/acmmp.hpp and the Python mirror in acmmp_b200/host.py are
+ * thin callers of this ABI.  No torch / C++ types cross this boundary.
+ *
+ * Conventions: every function returns 0 on success and a negative acmmp_status
+ * on failure (the reference prints and exit()s, ACMMP.cpp:67-100; here the
+ * caller decides).  acmmp_last_error() returns a static, human readable
+ * message for the last failure on that context (or the global one for
+ * context-less calls).  All host pointers are plain row-major arrays.
+ * Pointers named d_* are DEVICE pointers on the context's device.
+ */
+#ifndef ACMMP_B200_H_
+#define ACMMP_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ACMMP_MAX_SRC_VIEWS 32 /* 32-bit view mask, reference ACMMP.cu:76-84,437 */
+
+typedef enum {
+    ACMMP_OK = 0,
+    ACMMP_ERR_INVALID = -1, /* bad argument / call order */
+    ACMMP_ERR_CUDA = -2,    /* CUDA runtime failure (message in last_error) */
+    ACMMP_ERR_NO_DEVICE = -3,
+    ACMMP_ERR_STATE = -4    /* required input (images, depths, prior ...) missing */
+} acmmp_status;
+
+/* Bit-compatible with the reference `struct Camera`
+ * (/root/reference/src/acmmp_definitions.h:47-55): 100 bytes. */
+typedef struct {
+    float K[9];
+    float R[9];
+    float t[3];
+    int32_t height;
+    int32_t width;
+    float depth_min;
+    float depth_max;
+} acmmp_camera;
+
+/* Mirror of the reference `struct PatchMatchParams`
+ * (/root/reference/src/ACMMP.h:32-56).  Flags are int32 instead of bool so the
+ * layout is the same from C, C++ and ctypes. */
+typedef struct {
+    int32_t max_iterations;   /* 2 */
+    int32_t patch_size;       /* 11 */
+    int32_t num_images;       /* 1 reference + sources */
+    int32_t max_image_size;   /* 3200 */
+    int32_t radius_increment; /* 2 */
+    float sigma_spatial;      /* 5 */
+    float sigma_color;        /* 3 */
+    int32_t top_k;            /* 4 */
+    float baseline;           /* 0.54 */
+    float depth_min;
+    float depth_max;
+    float disparity_min;
+    float disparity_max;
+    float scaled_cols; /* float on purpose: ACMMP.h:47-48 */
+    float scaled_rows;
+    int32_t geom_consistency;
+    int32_t planar_prior;
+    int32_t multi_geometry;
+    int32_t hierarchy;
+    int32_t upsample;
+    int32_t seeded;
+} acmmp_params;
+
+/* How the uninitialised `plane_hypotheses_now` of the reference
+ * (ACMMP.cu:1149-1172) is given a meaning.  See DESIGN.md "UB pinning". */
+typedef enum {
+    /* what nvcc 12.9 -arch sm_100 made of it: in non-prior runs the pixel takes
+     * the best neighbour's plane whenever that arm exists (cost / depth / views
+     * only if it is cheaper); where the compiled code reads garbage registers
+     * the current plane is used instead. */
+    ACMMP_COMPAT_REF_SM100 = 0,
+    /* upstream GhiXu/ACMMP semantics: refine the current plane in place. */
+    ACMMP_COMPAT_UPSTREAM = 1
+} acmmp_compat_mode;
+
+typedef struct acmmp_ctx acmmp_ctx;
+
+/* ---- lifetime ------------------------------------------------------------
+ * replaces ACMMP::ACMMP / ~ACMMP (ACMMP.cpp:107-152) and cudaSetDevice(0)
+ * (acmmp_definitions.cpp:253). */
+int acmmp_create(acmmp_ctx **out, int device);
+void acmmp_destroy(acmmp_ctx *ctx);
+const char *acmmp_last_error(const acmmp_ctx *ctx);
+/* version / build info string ("acmmp_b200 <ver> sm_100a"). */
+const char *acmmp_version(void);
+
+/* default parameter block = PatchMatchParams{} (ACMMP.h:32-56). */
+void acmmp_default_params(acmmp_params *p);
+
+/* ---- mode setters ----------------------------------------------------------
+ * ACMMP::SetGeomConsistencyParams / SetHierarchyParams / SetPlanarPriorParams
+ * (ACMMP.cpp:447-464). */
+int acmmp_set_geom_consistency(acmmp_ctx *ctx, int multi_geometry);
+int acmmp_set_hierarchy(acmmp_ctx *ctx);
+int acmmp_set_planar_prior_params(acmmp_ctx *ctx);
+int acmmp_set_compat_mode(acmmp_ctx *ctx, int mode);
+int acmmp_get_params(const acmmp_ctx *ctx, acmmp_params *out);
+
+/* ---- inputs ----------------------------------------------------------------
+ * acmmp_set_problem: the upload half of ACMMP::InputInitialization +
+ * CudaSpaceInitialization (ACMMP.cpp:525-681): cameras[0] / images[0] are the
+ * reference view, 1..n-1 the sources, images already at this scale's size
+ * (cams[i].width x cams[i].height float32, row stride = width).  Widens the
+ * depth range by x0.6 / x1.2 exactly like ACMMP.cpp:600-601.  Allocates the
+ * per-pixel state.  `images[i]` may be a HOST pointer (images_on_device = 0)
+ * or a DEVICE pointer (1; used by the resident-pyramid path). */
+int acmmp_set_problem(acmmp_ctx *ctx, int n, const acmmp_camera *cams,
+                      const float *const *images, int images_on_device);
+
+/* geometric-consistency depth maps of ref + sources (ACMMP.cpp:608-635,
+ * 683-708): slot 0..n-1, size must equal that view's image size. */
+int acmmp_set_depth_map(acmmp_ctx *ctx, int slot, const float *depth, int w,
+                        int h, int on_device);
+
+/* warm start of a geometric-consistency run from the view's own previous
+ * result (ACMMP.cpp:710-742): depth, world-frame normals (3 floats / px),
+ * costs. */
+int acmmp_set_warm_start(acmmp_ctx *ctx, const float *depth,
+                         const float *normal3, const float *cost);
+
+/* hierarchy run inputs (ACMMP.cpp:745-808): coarse world-frame normals and
+ * coarse costs (cw x ch) and the JBU-upsampled depth at this scale. */
+int acmmp_set_hierarchy_inputs(acmmp_ctx *ctx, const float *coarse_normal3,
+                               const float *coarse_cost, int cw, int ch,
+                               const float *fine_depth);
+
+/* fixed per-pixel plane hypotheses (nx,ny,nz,d in the reference camera frame)
+ * = ACMMP::SetPlanarPrior, the reference's `seeded` branch (ACMMP.cpp:476-484,
+ * ACMMP.cu:634-639).  This is the parity hook of SURVEY 8(c). */
+int acmmp_set_seeded_planes(acmmp_ctx *ctx, const float *planes4);
+
+/* per-pixel prior planes + triangle labels =
+ * ACMMP::CudaPlanarPriorInitialization (ACMMP.cpp:811-831). */
+int acmmp_set_planar_prior(acmmp_ctx *ctx, const float *planes4,
+                           const uint32_t *mask);
+
+/* planar-prior construction on the current result (GetSupportPoints ->
+ * DelaunayTriangulation -> raster + GetPriorPlaneParams -> range check ->
+ * CudaPlanarPriorInitialization; ACMMP.cpp:868-958,
+ * acmmp_definitions.cpp:306-378).  Outputs are optional (may be NULL). */
+int acmmp_build_planar_prior(acmmp_ctx *ctx, int *num_support,
+                             int *num_triangles);
+
+/* ---- run -------------------------------------------------------------------
+ * ACMMP::RunPatchMatch (ACMMP.cu:1378-1456).  `seed` replaces the reference's
+ * clock64() seed (ACMMP.cu:624).  Runs on the context's stream; results are
+ * in device memory until fetched. */
+int acmmp_run(acmmp_ctx *ctx, uint64_t seed);
+
+/* the same sequence in separately callable steps (parity tests) */
+int acmmp_run_init(acmmp_ctx *ctx, uint64_t seed);        /* RandomInitialization */
+int acmmp_run_sweep(acmmp_ctx *ctx, int iter, int color); /* 0 = black, 1 = red  */
+int acmmp_run_tail(acmmp_ctx *ctx); /* GetDepthandNormal + Black/RedPixelFilter */
+
+/* ---- outputs ---------------------------------------------------------------
+ * ACMMP::GetPlaneHypothesis / GetCost (ACMMP.cpp:848-856): planes4 is
+ * (nx,ny,nz,w) per pixel - after acmmp_run / acmmp_run_tail the normal is in
+ * the WORLD frame and w is the depth.  Any pointer may be NULL. */
+int acmmp_get_result(acmmp_ctx *ctx, float *planes4, float *cost,
+                     uint32_t *selected_views);
+/* the same split into the .dmb layouts (depth h*w, normal h*w*3, cost h*w). */
+int acmmp_get_maps(acmmp_ctx *ctx, float *depth, float *normal3, float *cost);
+/* device pointer of the current float depth map (valid after run/tail) for the
+ * NCCL exchange; w*h floats. */
+int acmmp_get_depth_device(acmmp_ctx *ctx, const float **d_depth);
+
+/* raw state access for step-exact parity tests: planes (4 f32), costs,
+ * selected views, rng state (6 x u32: d, v0..v4).  NULL = skip. */
+int acmmp_get_state(acmmp_ctx *ctx, float *planes4, float *cost,
+                    uint32_t *selected_views, uint32_t *rng6);
+int acmmp_set_state(acmmp_ctx *ctx, const float *planes4, const float *cost,
+                    const uint32_t *selected_views, const uint32_t *rng6);
+
+int acmmp_width(const acmmp_ctx *ctx);
+int acmmp_height(const acmmp_ctx *ctx);
+int acmmp_sync(acmmp_ctx *ctx);
+/* kernels launched by this context since creation (bench `gpu_launches`). */
+uint64_t acmmp_launch_count(const acmmp_ctx *ctx);
+/* device time of the last acmmp_run in ms, split per kernel family:
+ * out[0]=init out[1]=sweeps out[2]=tail out[3]=total (CUDA events). */
+int acmmp_last_timing(acmmp_ctx *ctx, float out[4]);
+
+/* ---- JBU ---------------------------------------------------------------------
+ * RunJBU / JBU::CudaRun / JBU_cu (ACMMP.cpp:1022-1087, ACMMP.cu:1458-1549):
+ * joint bilateral upsample of a (sw x sh) depth map to (w x h) guided by the
+ * (w x h) image.  Returns 1 (and writes nothing) when the integer scale is 1,
+ * like the reference's early-out. */
+int acmmp_jbu_depth(int device, const float *image, int w, int h,
+                    const float *depth, int sw, int sh, float *out);
+
+/* ---- image pyramid -----------------------------------------------------------
+ * cv::resize(..., INTER_LINEAR) of a float image as used by
+ * ACMMP::InputInitialization (ACMMP.cpp:566-598) and
+ * JointBilateralUpsampling (acmmp_definitions.cpp:428-435); host in / host
+ * out, computed on the device. */
+int acmmp_resize_linear(int device, const float *src, int sw, int sh,
+                        float *dst, int dw, int dh);
+
+/* ---- RNG ---------------------------------------------------------------------
+ * XORWOW state of curand_init(seed, subsequence=y, offset=x) for every pixel
+ * of a w x h image (ACMMP.cu:624), 6 x u32 per pixel (d, v0..v4); host out. */
+int acmmp_rng_init_states(int device, uint64_t seed, int w, int h,
+                          uint32_t *rng6);
+
+/* ---- micro-benchmarks used by bench.py for the roofline denominators --------
+ * measured FP32 FMA throughput (TFLOP/s), MUFU rate (Gop/s). */
+int acmmp_measure_fp32_peak(int device, double *tflops, double *mufu_gops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ACMMP_B200_H_ */

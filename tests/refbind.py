@@ -1,0 +1,157 @@
+"""ctypes binding of oracle/_ref/libacmmp_ref.so - the REFERENCE's own CUDA kernels
+behind a C ABI (oracle/ref_harness.cu).  Test infrastructure: used by tests/,
+tools/gpu_parity.py and bench.py --impl reference only."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from acmmp_b200 import lib as L
+
+REF_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle", "_ref", "libacmmp_ref.so")
+
+
+def available():
+    return os.path.exists(REF_PATH)
+
+
+_ref = None
+
+
+def load():
+    global _ref
+    if _ref is None:
+        lib = C.CDLL(REF_PATH)
+        vp, fp, up = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32)
+        lib.ref_create.argtypes = [C.POINTER(vp), C.c_int]
+        lib.ref_destroy.argtypes = [vp]
+        lib.ref_destroy.restype = None
+        lib.ref_last_error.argtypes = [vp]
+        lib.ref_last_error.restype = C.c_char_p
+        lib.ref_set_problem.argtypes = [vp, C.c_int, C.POINTER(L.Camera), C.POINTER(vp)]
+        lib.ref_set_flags.argtypes = [vp] + [C.c_int] * 6 + [C.c_float, C.c_float]
+        lib.ref_set_depth_map.argtypes = [vp, C.c_int, fp, C.c_int, C.c_int]
+        lib.ref_set_planes.argtypes = [vp, C.c_int, fp, C.c_int]
+        lib.ref_set_scalars.argtypes = [vp, C.c_int, vp]
+        lib.ref_set_rng.argtypes = [vp, up]
+        lib.ref_get_state.argtypes = [vp, fp, fp, up, up, fp]
+        lib.ref_run_init.argtypes = [vp, C.c_uint64]
+        lib.ref_run_sweep.argtypes = [vp, C.c_int, C.c_int]
+        lib.ref_run_tail.argtypes = [vp]
+        lib.ref_run.argtypes = [vp, C.c_uint64]
+        lib.ref_last_ms.argtypes = [vp]
+        lib.ref_last_ms.restype = C.c_float
+        lib.ref_ncc.argtypes = [vp, fp, C.c_int, fp]
+        lib.ref_homography.argtypes = [vp, fp, C.c_int, C.c_int, fp]
+        lib.ref_geom_cost.argtypes = [vp, fp, C.c_int, fp]
+        lib.ref_jbu.argtypes = [fp, C.c_int, C.c_int, fp, C.c_int, C.c_int, fp]
+        _ref = lib
+    return _ref
+
+
+class RefACMMP:
+    """The reference kernels driven like the reference's class ACMMP."""
+
+    def __init__(self, device=0):
+        self.lib = load()
+        self.ctx = C.c_void_p()
+        if self.lib.ref_create(C.byref(self.ctx), device) != 0:
+            raise RuntimeError("ref_create failed")
+        self.flags = dict(geom=0, planar_prior=0, multi_geometry=0, hierarchy=0, upsample=0, seeded=0,
+                          scaled_cols=0.0, scaled_rows=0.0)
+
+    def close(self):
+        if self.ctx:
+            self.lib.ref_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise RuntimeError(f"{what}: {self.lib.ref_last_error(self.ctx).decode()}")
+
+    def set_problem(self, images, cams):
+        n = len(images)
+        self.imgs = [L.f32(i) for i in images]
+        self.h, self.w = self.imgs[0].shape
+        cam_arr = (L.Camera * n)(*[c.copy() for c in cams])
+        ptrs = (C.c_void_p * n)(*[im.ctypes.data for im in self.imgs])
+        self._ck(self.lib.ref_set_problem(self.ctx, n, cam_arr, ptrs), "ref_set_problem")
+        self._push_flags()
+
+    def _push_flags(self):
+        f = self.flags
+        self.lib.ref_set_flags(self.ctx, f["geom"], f["planar_prior"], f["multi_geometry"], f["hierarchy"], f["upsample"],
+                               f["seeded"], f["scaled_cols"], f["scaled_rows"])
+
+    def set_flags(self, **kw):
+        self.flags.update(kw)
+        self._push_flags()
+
+    def set_depth_map(self, slot, depth):
+        d = L.f32(depth)
+        self._ck(self.lib.ref_set_depth_map(self.ctx, slot, L.fptr(d), d.shape[1], d.shape[0]), "ref_set_depth_map")
+
+    def set_planes(self, which, planes):
+        p = L.f32(planes)
+        self._ck(self.lib.ref_set_planes(self.ctx, which, L.fptr(p), p.size // 4), "ref_set_planes")
+
+    def set_scalars(self, which, arr):
+        a = np.ascontiguousarray(arr)
+        assert a.itemsize == 4
+        self._ck(self.lib.ref_set_scalars(self.ctx, which, a.ctypes.data), "ref_set_scalars")
+
+    def set_rng(self, rng6):
+        r = np.ascontiguousarray(rng6, np.uint32)
+        self._ck(self.lib.ref_set_rng(self.ctx, L.uptr(r)), "ref_set_rng")
+
+    def get_state(self):
+        planes = np.empty((self.h, self.w, 4), np.float32)
+        costs = np.empty((self.h, self.w), np.float32)
+        sel = np.empty((self.h, self.w), np.uint32)
+        rng = np.empty((self.h, self.w, 6), np.uint32)
+        pre = np.empty((self.h, self.w), np.float32)
+        self._ck(self.lib.ref_get_state(self.ctx, L.fptr(planes), L.fptr(costs), L.uptr(sel), L.uptr(rng), L.fptr(pre)), "ref_get_state")
+        return planes, costs, sel, rng, pre
+
+    def run_init(self, seed):
+        self._ck(self.lib.ref_run_init(self.ctx, seed), "ref_run_init")
+
+    def run_sweep(self, it, color):
+        self._ck(self.lib.ref_run_sweep(self.ctx, it, color), "ref_run_sweep")
+
+    def run_tail(self):
+        self._ck(self.lib.ref_run_tail(self.ctx), "ref_run_tail")
+
+    def run(self, seed):
+        self._ck(self.lib.ref_run(self.ctx, seed), "ref_run")
+        return float(self.lib.ref_last_ms(self.ctx))
+
+    def ncc(self, planes, view):
+        p = L.f32(planes)
+        out = np.empty((self.h, self.w), np.float32)
+        self._ck(self.lib.ref_ncc(self.ctx, L.fptr(p), view, L.fptr(out)), "ref_ncc")
+        return out
+
+    def homography(self, planes, view):
+        p = L.f32(planes).reshape(-1, 4)
+        out = np.empty((p.shape[0], 9), np.float32)
+        self._ck(self.lib.ref_homography(self.ctx, L.fptr(p), p.shape[0], view, L.fptr(out)), "ref_homography")
+        return out
+
+    def geom_cost(self, planes, view):
+        p = L.f32(planes)
+        out = np.empty((self.h, self.w), np.float32)
+        self._ck(self.lib.ref_geom_cost(self.ctx, L.fptr(p), view, L.fptr(out)), "ref_geom_cost")
+        return out
+
+
+def ref_jbu(image, depth):
+    lib = load()
+    img, dep = L.f32(image), L.f32(depth)
+    out = np.empty_like(img)
+    rc = lib.ref_jbu(L.fptr(img), img.shape[1], img.shape[0], L.fptr(dep), dep.shape[1], dep.shape[0], L.fptr(out))
+    if rc == 1:
+        return None
+    if rc != 0:
+        raise RuntimeError("ref_jbu failed")
+    return out
