@@ -44,10 +44,12 @@ struct DevBuf {
     template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
-struct ViewImage {
+// All views of a problem live in ONE layered cudaArray (layer i = view i) behind
+// one texture object, so kernels sample any view through a warp-uniform handle.
+struct LayeredImages {
     cudaArray_t arr = nullptr;
     cudaTextureObject_t tex = 0;
-    int w = 0, h = 0;
+    int w = 0, h = 0, layers = 0;
 };
 
 }  // namespace
@@ -62,10 +64,10 @@ struct acmmp_ctx {
     int n = 0;   // images in the problem
     int W = 0, H = 0;
     std::vector<acmmp_camera> cams;
-    std::vector<ViewImage> views;
+    LayeredImages views;
     std::vector<DevBuf> depth_maps;   // per slot
     std::vector<int> depth_set;
-    DevBuf ref_image, d_cams, d_tex, d_depth_ptrs, d_rc, d_pairs;
+    DevBuf ref_image, d_cams, d_depth_ptrs, d_rc, d_pairs, stage_in, stage_pad;
     DevBuf planes, costs, pre_costs, sel, rng, planes_snap, costs_snap;
     DevBuf seeded, prior_planes, plane_masks, scaled_planes, tmp_a, tmp_b, tmp_c;
     bool have_seeded = false, have_prior = false, have_scaled = false, have_warm = false;
@@ -101,37 +103,63 @@ int bind_device(acmmp_ctx *ctx) {
     return 0;
 }
 
-void destroy_view(ViewImage &v) {
+void destroy_views(LayeredImages &v) {
     if (v.tex) cudaDestroyTextureObject(v.tex);
     if (v.arr) cudaFreeArray(v.arr);
-    v = ViewImage();
+    v = LayeredImages();
 }
 
-// cudaArray + texture object with the reference's descriptor (ACMMP.cpp:646-663):
-// float, linear filter, unnormalised coordinates, "wrap" (not honoured for
-// unnormalised coordinates: the hardware clamps).
-int make_view(acmmp_ctx *ctx, ViewImage &v, const float *img, int w, int h, bool on_device) {
-    if (v.w != w || v.h != h || !v.arr) {
-        destroy_view(v);
-        cudaChannelFormatDesc desc = cudaCreateChannelDesc(32, 0, 0, 0, cudaChannelFormatKindFloat);
-        CU(ctx, cudaMallocArray(&v.arr, &desc, w, h));
-        cudaResourceDesc res;
-        memset(&res, 0, sizeof res);
-        res.resType = cudaResourceTypeArray;
-        res.res.array.array = v.arr;
-        cudaTextureDesc td;
-        memset(&td, 0, sizeof td);
-        td.addressMode[0] = cudaAddressModeWrap;
-        td.addressMode[1] = cudaAddressModeWrap;
-        td.filterMode = cudaFilterModeLinear;
-        td.readMode = cudaReadModeElementType;
-        td.normalizedCoords = 0;
-        CU(ctx, cudaCreateTextureObject(&v.tex, &res, &td, nullptr));
-        v.w = w;
-        v.h = h;
+// layered float array + texture object with the reference's sampling state
+// (ACMMP.cpp:646-663): linear filter, unnormalised coordinates, "wrap" (not
+// honoured for unnormalised coordinates: the hardware clamps).
+int ensure_views(acmmp_ctx *ctx, int w, int h, int layers) {
+    LayeredImages &v = ctx->views;
+    if (v.arr && v.w == w && v.h == h && v.layers >= layers) return 0;
+    destroy_views(v);
+    cudaChannelFormatDesc desc = cudaCreateChannelDesc(32, 0, 0, 0, cudaChannelFormatKindFloat);
+    CU(ctx, cudaMalloc3DArray(&v.arr, &desc, make_cudaExtent(w, h, layers), cudaArrayLayered));
+    cudaResourceDesc res;
+    memset(&res, 0, sizeof res);
+    res.resType = cudaResourceTypeArray;
+    res.res.array.array = v.arr;
+    cudaTextureDesc td;
+    memset(&td, 0, sizeof td);
+    td.addressMode[0] = cudaAddressModeWrap;
+    td.addressMode[1] = cudaAddressModeWrap;
+    td.filterMode = cudaFilterModeLinear;
+    td.readMode = cudaReadModeElementType;
+    td.normalizedCoords = 0;
+    CU(ctx, cudaCreateTextureObject(&v.tex, &res, &td, nullptr));
+    v.w = w;
+    v.h = h;
+    v.layers = layers;
+    return 0;
+}
+
+int upload_layer(acmmp_ctx *ctx, int layer, const float *img, int w, int h, bool on_device) {
+    const LayeredImages &v = ctx->views;
+    const float *d_src = img;
+    if (!on_device) {
+        CU(ctx, ctx->stage_in.ensure((size_t)w * h * sizeof(float)));
+        CU(ctx, cudaMemcpyAsync(ctx->stage_in.p, img, (size_t)w * h * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+        d_src = ctx->stage_in.as<float>();
     }
-    CU(ctx, cudaMemcpy2DToArrayAsync(v.arr, 0, 0, img, (size_t)w * sizeof(float), (size_t)w * sizeof(float), h,
-                                     on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
+    if (w != v.w || h != v.h) {   // smaller than the layer: replicate the edges
+        CU(ctx, ctx->stage_pad.ensure((size_t)v.w * v.h * sizeof(float)));
+        CU(ctx, launch_pad_replicate(d_src, w, h, ctx->stage_pad.as<float>(), v.w, v.h, ctx->stream));
+        ctx->launches++;
+        d_src = ctx->stage_pad.as<float>();
+    }
+    cudaMemcpy3DParms cp;
+    memset(&cp, 0, sizeof cp);
+    cp.srcPtr = make_cudaPitchedPtr(const_cast<float *>(d_src), (size_t)v.w * sizeof(float), v.w, v.h);
+    cp.dstArray = v.arr;
+    cp.dstPos = make_cudaPos(0, 0, layer);
+    cp.extent = make_cudaExtent(v.w, v.h, 1);
+    cp.kind = cudaMemcpyDeviceToDevice;
+    CU(ctx, cudaMemcpy3DAsync(&cp, ctx->stream));
+    // staging buffers are reused by the next layer
+    if (!on_device || w != v.w || h != v.h) CU(ctx, cudaStreamSynchronize(ctx->stream));
     return 0;
 }
 
@@ -146,24 +174,18 @@ int init_mode(const acmmp_params &p) {
 int refresh_pairs(acmmp_ctx *ctx) {
     if (!ctx->pairs_dirty) return 0;
     const int n = ctx->n;
-    std::vector<cudaTextureObject_t> tex(n);
     std::vector<const float *> dptr(n, nullptr);
-    for (int i = 0; i < n; ++i) {
-        tex[i] = ctx->views[i].tex;
+    for (int i = 0; i < n; ++i)
         if (i < (int)ctx->depth_maps.size() && ctx->depth_set[i]) dptr[i] = ctx->depth_maps[i].as<float>();
-    }
     CU(ctx, ctx->d_cams.ensure(sizeof(acmmp_camera) * n));
-    CU(ctx, ctx->d_tex.ensure(sizeof(cudaTextureObject_t) * n));
     CU(ctx, ctx->d_depth_ptrs.ensure(sizeof(float *) * n));
     CU(ctx, ctx->d_rc.ensure(ref_const_size()));
     CU(ctx, ctx->d_pairs.ensure(pair_const_size() * (n > 1 ? n - 1 : 1)));
     // small synchronous copies from pageable host vectors: safe w.r.t. lifetime
     CU(ctx, cudaMemcpyAsync(ctx->d_cams.p, ctx->cams.data(), sizeof(acmmp_camera) * n, cudaMemcpyHostToDevice, ctx->stream));
-    CU(ctx, cudaMemcpyAsync(ctx->d_tex.p, tex.data(), sizeof(cudaTextureObject_t) * n, cudaMemcpyHostToDevice, ctx->stream));
     CU(ctx, cudaMemcpyAsync(ctx->d_depth_ptrs.p, dptr.data(), sizeof(float *) * n, cudaMemcpyHostToDevice, ctx->stream));
     CU(ctx, cudaStreamSynchronize(ctx->stream));
-    CU(ctx, launch_setup_pairs(ctx->d_cams.as<acmmp_camera>(), n, ctx->d_tex.as<cudaTextureObject_t>(),
-                               ctx->d_depth_ptrs.as<const float *>(), ctx->params.depth_min, ctx->params.depth_max,
+    CU(ctx, launch_setup_pairs(ctx->d_cams.as<acmmp_camera>(), n, ctx->d_depth_ptrs.as<const float *>(), ctx->params.depth_min, ctx->params.depth_max,
                                ctx->d_rc.as<RefConst>(), ctx->d_pairs.as<PairConst>(), ctx->stream));
     ctx->launches++;
     ctx->pairs_dirty = false;
@@ -217,9 +239,9 @@ void acmmp_destroy(acmmp_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    for (auto &v : ctx->views) destroy_view(v);
+    destroy_views(ctx->views);
     for (auto &d : ctx->depth_maps) d.release();
-    DevBuf *bufs[] = {&ctx->ref_image, &ctx->d_cams, &ctx->d_tex, &ctx->d_depth_ptrs, &ctx->d_rc, &ctx->d_pairs,
+    DevBuf *bufs[] = {&ctx->ref_image, &ctx->d_cams, &ctx->stage_in, &ctx->stage_pad, &ctx->d_depth_ptrs, &ctx->d_rc, &ctx->d_pairs,
                       &ctx->planes, &ctx->costs, &ctx->pre_costs, &ctx->sel, &ctx->rng, &ctx->planes_snap,
                       &ctx->costs_snap, &ctx->seeded, &ctx->prior_planes, &ctx->plane_masks, &ctx->scaled_planes,
                       &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c};
@@ -284,9 +306,17 @@ int acmmp_set_problem(acmmp_ctx *ctx, int n, const acmmp_camera *cams, const flo
     if (bind_device(ctx)) return ACMMP_ERR_CUDA;
     ctx->n = n;
     ctx->cams.assign(cams, cams + n);
-    if ((int)ctx->views.size() < n) ctx->views.resize(n);
+    int maxw = 0, maxh = 0;
     for (int i = 0; i < n; ++i) {
-        int rcode = make_view(ctx, ctx->views[i], images[i], cams[i].width, cams[i].height, images_on_device != 0);
+        if (cams[i].width > maxw) maxw = cams[i].width;
+        if (cams[i].height > maxh) maxh = cams[i].height;
+    }
+    {
+        int rcode = ensure_views(ctx, maxw, maxh, n);
+        if (rcode) return rcode;
+    }
+    for (int i = 0; i < n; ++i) {
+        int rcode = upload_layer(ctx, i, images[i], cams[i].width, cams[i].height, images_on_device != 0);
         if (rcode) return rcode;
     }
     ctx->W = cams[0].width;

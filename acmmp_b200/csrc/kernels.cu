@@ -25,8 +25,7 @@ ACMMP_DEV float dot3_ref_order(float a0, float b0, float a1, float b1, float a2,
     return ffma(a2, b2, ffma(a0, b0, fmul(a1, b1)));
 }
 
-__global__ void setup_pairs_kernel(const acmmp_camera *cams, int n, const cudaTextureObject_t *tex,
-                                   const float *const *depth_maps, float depth_min, float depth_max,
+__global__ void setup_pairs_kernel(const acmmp_camera *cams, int n, const float *const *depth_maps, float depth_min, float depth_max,
                                    RefConst *rc_out, PairConst *pairs_out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const acmmp_camera &r = cams[0];
@@ -64,7 +63,7 @@ __global__ void setup_pairs_kernel(const acmmp_camera *cams, int n, const cudaTe
         pc.trel[a] = dot3_ref_order(s.R[3 * a + 0], c0, s.R[3 * a + 1], c1, s.R[3 * a + 2], c2);
     pc.K0s = s.K[0]; pc.K2s = s.K[2]; pc.K4s = s.K[4]; pc.K5s = s.K[5]; pc.K8s = s.K[8];
     pc.ws = (float)s.width; pc.hs = (float)s.height; pc.pad = 0.0f;
-    pc.tex = tex[i + 1];
+    pc.layer = i + 1; pc.pad2 = 0;
     for (int k = 0; k < 9; ++k) { pc.Rs[k] = s.R[k]; pc.Ks[k] = s.K[k]; }
     for (int k = 0; k < 3; ++k) pc.ts[k] = s.t[k];
     pc.Cs[0] = -nsc0; pc.Cs[1] = -nsc1; pc.Cs[2] = -nsc2;
@@ -249,6 +248,16 @@ __global__ void resize_linear_kernel(const float *src, int sw, int sh, float *ds
     dst[(size_t)dy * dw + dx] = fadd(fmul(r0, b0), fmul(r1, b1));
 }
 
+// image -> padded layer staging buffer with replicated edges: sampling the
+// (larger) layer with clamp addressing is then identical to clamp addressing on
+// the image itself.
+__global__ void pad_replicate_kernel(const float *src, int w, int h, float *dst, int W, int H) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= W || y >= H) return;
+    dst[(size_t)y * W + x] = src[(size_t)min(y, h - 1) * w + min(x, w - 1)];
+}
+
 // ---------------------------------------------------------------------------
 // roofline denominators: FP32 FMA and MUFU issue rate of this chip
 // ---------------------------------------------------------------------------
@@ -281,10 +290,9 @@ __global__ void mufu_peak_kernel(float *out, int iters) {
 // ===========================================================================
 static inline dim3 grid2(int w, int h, int bx, int by) { return dim3((w + bx - 1) / bx, (h + by - 1) / by, 1); }
 
-cudaError_t launch_setup_pairs(const acmmp_camera *d_cams, int n, const cudaTextureObject_t *d_tex,
-                               const float *const *d_depth_maps, float depth_min, float depth_max,
+cudaError_t launch_setup_pairs(const acmmp_camera *d_cams, int n, const float *const *d_depth_maps, float depth_min, float depth_max,
                                RefConst *d_rc, PairConst *d_pairs, cudaStream_t st) {
-    setup_pairs_kernel<<<1, 64, 0, st>>>(d_cams, n, d_tex, d_depth_maps, depth_min, depth_max, d_rc, d_pairs);
+    setup_pairs_kernel<<<1, 64, 0, st>>>(d_cams, n, d_depth_maps, depth_min, depth_max, d_rc, d_pairs);
     return cudaGetLastError();
 }
 
@@ -310,7 +318,7 @@ cudaError_t launch_init(const InitLaunch &L, cudaStream_t st) {
     a.seeded_planes = L.seeded_planes; a.prior_planes = L.prior_planes; a.plane_masks = L.plane_masks;
     a.scaled_planes = L.scaled_planes;
     a.rng = RngPlanes{L.rng6, (size_t)L.W * L.H};
-    a.ref_image = L.ref_image; a.pairs = L.pairs; a.rc = L.rc; a.nsrc = L.nsrc; a.mode = L.mode;
+    a.ref_image = L.ref_image; a.tex = L.tex; a.pairs = L.pairs; a.rc = L.rc; a.nsrc = L.nsrc; a.mode = L.mode;
     a.hierarchy = L.hierarchy; a.top_k = L.top_k; a.sigma_spatial = L.sigma_spatial; a.sigma_color = L.sigma_color;
     a.scaled_cols = L.scaled_cols; a.scaled_rows = L.scaled_rows;
     const size_t smem = init_smem_bytes(L.nsrc);
@@ -330,7 +338,7 @@ cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st) {
     a.selected_views = L.selected_views; a.pre_costs = L.pre_costs; a.prior_planes = L.prior_planes;
     a.plane_masks = L.plane_masks;
     a.rng = RngPlanes{L.rng6, (size_t)L.W * L.H};
-    a.ref_image = L.ref_image; a.pairs = L.pairs; a.rc = L.rc; a.nsrc = L.nsrc; a.iter = L.iter; a.color = L.color;
+    a.ref_image = L.ref_image; a.tex = L.tex; a.pairs = L.pairs; a.rc = L.rc; a.nsrc = L.nsrc; a.iter = L.iter; a.color = L.color;
     a.sigma_spatial = L.sigma_spatial; a.sigma_color = L.sigma_color;
     a.geom_consistency = L.geom_consistency; a.planar_prior = L.planar_prior; a.hierarchy = L.hierarchy;
     a.compat = L.compat;
@@ -374,6 +382,11 @@ cudaError_t launch_jbu_depth(const float *image, int w, int h, const float *sdep
 
 cudaError_t launch_resize_linear(const float *src, int sw, int sh, float *dst, int dw, int dh, cudaStream_t st) {
     resize_linear_kernel<<<grid2(dw, dh, 32, 8), dim3(32, 8), 0, st>>>(src, sw, sh, dst, dw, dh);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pad_replicate(const float *src, int w, int h, float *dst, int W, int H, cudaStream_t st) {
+    pad_replicate_kernel<<<grid2(W, H, 32, 8), dim3(32, 8), 0, st>>>(src, w, h, dst, W, H);
     return cudaGetLastError();
 }
 

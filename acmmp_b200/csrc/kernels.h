@@ -21,6 +21,7 @@ struct InitLaunch {
     const float4 *scaled_planes;
     uint32_t *rng6;
     const float *ref_image;
+    cudaTextureObject_t tex;
     const PairConst *pairs;
     const RefConst *rc;
     int W, H, nsrc, mode, hierarchy, top_k;
@@ -38,6 +39,7 @@ struct SweepLaunch {
     const uint32_t *plane_masks;
     uint32_t *rng6;
     const float *ref_image;
+    cudaTextureObject_t tex;
     const PairConst *pairs;
     const RefConst *rc;
     int W, H, nsrc, iter, color;
@@ -45,8 +47,7 @@ struct SweepLaunch {
     int geom_consistency, planar_prior, hierarchy, compat;
 };
 
-cudaError_t launch_setup_pairs(const acmmp_camera *d_cams, int n, const cudaTextureObject_t *d_tex,
-                               const float *const *d_depth_maps, float depth_min, float depth_max,
+cudaError_t launch_setup_pairs(const acmmp_camera *d_cams, int n, const float *const *d_depth_maps, float depth_min, float depth_max,
                                RefConst *d_rc, PairConst *d_pairs, cudaStream_t st);
 cudaError_t launch_rng_init(unsigned long long seed, int W, int H, uint32_t *d_rng6, cudaStream_t st);
 cudaError_t launch_init(const InitLaunch &L, cudaStream_t st);
@@ -59,6 +60,7 @@ cudaError_t launch_pack_planes(float4 *planes, int n, const float *normal3, cons
 cudaError_t launch_jbu_depth(const float *image, int w, int h, const float *sdepth, int sw, int sh, int scale,
                              float *out, cudaStream_t st);
 cudaError_t launch_resize_linear(const float *src, int sw, int sh, float *dst, int dw, int dh, cudaStream_t st);
+cudaError_t launch_pad_replicate(const float *src, int w, int h, float *dst, int W, int H, cudaStream_t st);
 cudaError_t launch_fp32_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
 cudaError_t launch_mufu_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
 size_t pair_const_size();

@@ -50,6 +50,7 @@ struct SweepArgs {
     const uint32_t *plane_masks;
     RngPlanes rng;
     const float *ref_image;   // row-major reference image
+    cudaTextureObject_t tex;  // layered texture of all views (uniform handle)
     const PairConst *pairs;   // nsrc
     const RefConst *rc;
     int nsrc;

@@ -125,7 +125,7 @@ def main():
         except Exception as e:  # keep going: every section is independent evidence
             out[name] = {"error": repr(e), "trace": traceback.format_exc()[-1500:]}
         out[name + "_s"] = round(time.time() - t, 2)
-        print(f"== {name}: {json.dumps(out[name])[:1200]}", flush=True)
+        print(f"== {name}: {json.dumps(out[name])[:3000]}", flush=True)
         save()
 
     rs = np.random.default_rng(0)
@@ -184,7 +184,7 @@ def main():
     section("random_init", s_random)
 
     # ---- 4. step-exact half sweeps from identical state --------------------------------
-    def sweep_compare(flags_desc):
+    def sweep_compare(flags_desc, masks=None):
         res = {}
         for it in (0, 1):
             for color in (0, 1):
@@ -194,15 +194,39 @@ def main():
                 mine.run_sweep(it, color)
                 rp, rc_, rsel, rrng, _ = ref.get_state()
                 mp, mc, msel, mrng = mine.get_state()
+                # the reference once more from the same state: its own determinism
+                ref.set_planes(0, rp0); ref.set_scalars(0, rc0); ref.set_scalars(2, rsel0); ref.set_rng(rrng0)
+                ref.run_sweep(it, color)
+                rp2 = ref.get_state()[0]
                 cm = color_mask(h, w, color)
                 inner = cm & interior(h, w, 4)
-                res[f"it{it}_c{color}"] = {
+                same = (bits(mp) == bits(rp)).all(-1)
+                bad = inner & ~same
+                ys, xs = np.nonzero(bad)
+                r = {
                     "plane_bit_equal_all": plane_stats(mp, rp, cm),
                     "plane_bit_equal_interior": plane_stats(mp, rp, inner),
+                    "ref_rerun_bit_equal_interior": plane_stats(rp2, rp, inner),
                     "cost": cmp_f32(mc, rc_, inner), "mask_equal": float((msel == rsel)[inner].mean()),
                     "rng_equal": float((mrng == rrng).all(-1)[inner].mean()),
                     "other_colour_untouched": plane_stats(mp, rp0, ~cm),
+                    "n_bad": int(bad.sum()),
+                    "bad_y_mod32": np.bincount(ys % 32, minlength=32).tolist(),
+                    "bad_x_mod32": np.bincount(xs % 32, minlength=32).tolist(),
+                    "bad_cost_equal_frac": float((bits(mc) == bits(rc_))[bad].mean()) if bad.any() else 1.0,
+                    "bad_rng_equal_frac": float((mrng == rrng).all(-1)[bad].mean()) if bad.any() else 1.0,
                 }
+                if masks is not None:
+                    r["equal_mask_pos"] = plane_stats(mp, rp, inner & (masks > 0))
+                    r["equal_mask_zero"] = plane_stats(mp, rp, inner & (masks == 0))
+                samples = []
+                for k in range(min(6, len(ys))):
+                    y, x = int(ys[k * max(1, len(ys) // 6)]), int(xs[k * max(1, len(ys) // 6)])
+                    samples.append({"xy": [x, y], "mine": mp[y, x].tolist() + [float(mc[y, x])],
+                                    "ref": rp[y, x].tolist() + [float(rc_[y, x])],
+                                    "before": rp0[y, x].tolist() + [float(rc0[y, x])]})
+                r["samples"] = samples
+                res[f"it{it}_c{color}"] = r
         return res
 
     def s_sweeps():
@@ -293,7 +317,7 @@ def main():
         r1, m1 = ref.get_state(), m.get_state()
         mine = m
         res = {"init_plane_bit_equal": plane_stats(m1[0], r1[0])}
-        res.update(sweep_compare("prior"))
+        res.update(sweep_compare("prior", masks))
         return res
     section("sweeps_prior", s_prior)
 
