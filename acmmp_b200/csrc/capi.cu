@@ -69,7 +69,8 @@ struct acmmp_ctx {
     std::vector<int> depth_set;
     DevBuf ref_image, d_cams, d_depth_ptrs, d_rc, d_pairs, stage_in, stage_pad;
     DevBuf planes, costs, pre_costs, sel, rng, planes_snap, costs_snap;
-    DevBuf seeded, prior_planes, plane_masks, scaled_planes, tmp_a, tmp_b, tmp_c;
+    DevBuf seeded, prior_planes, plane_masks, scaled_planes, tmp_a, tmp_b, tmp_c, tri_buf;
+    std::vector<int32_t> h_cells, h_tris;
     bool have_seeded = false, have_prior = false, have_scaled = false, have_warm = false;
     bool pairs_dirty = true;
     bool tail_done = false;
@@ -244,7 +245,7 @@ void acmmp_destroy(acmmp_ctx *ctx) {
     DevBuf *bufs[] = {&ctx->ref_image, &ctx->d_cams, &ctx->stage_in, &ctx->stage_pad, &ctx->d_depth_ptrs, &ctx->d_rc, &ctx->d_pairs,
                       &ctx->planes, &ctx->costs, &ctx->pre_costs, &ctx->sel, &ctx->rng, &ctx->planes_snap,
                       &ctx->costs_snap, &ctx->seeded, &ctx->prior_planes, &ctx->plane_masks, &ctx->scaled_planes,
-                      &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c};
+                      &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c, &ctx->tri_buf};
     for (auto *b : bufs) b->release();
     for (auto &ev : ctx->ev)
         if (ev) cudaEventDestroy(ev);

@@ -11,6 +11,7 @@
 
 #include "init_kernel.cu.inc"
 #include "sweep_kernel.cu.inc"
+#include "prior_kernels.cu.inc"
 
 namespace acmmp {
 

@@ -63,6 +63,11 @@ cudaError_t launch_resize_linear(const float *src, int sw, int sh, float *dst, i
 cudaError_t launch_pad_replicate(const float *src, int w, int h, float *dst, int W, int H, cudaStream_t st);
 cudaError_t launch_fp32_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
 cudaError_t launch_mufu_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
+cudaError_t launch_support_cells(const float *costs, int W, int H, int2 *cells, cudaStream_t st);
+cudaError_t launch_tri_raster(const int *tris, int ntri, const float4 *planes, const RefConst *rc, int W,
+                              float4 *tri_planes, unsigned *labels, cudaStream_t st);
+cudaError_t launch_prior_finalize(const unsigned *labels, const float4 *tri_planes, const RefConst *rc, int W, int H,
+                                  float4 *prior_planes, unsigned *masks, cudaStream_t st);
 size_t pair_const_size();
 size_t ref_const_size();
 

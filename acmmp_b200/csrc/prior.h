@@ -1,18 +1,21 @@
-// prior.h - planar-prior construction from the current depth/cost maps (host).
+// prior.h - planar-prior construction from the current depth/cost maps.
 // Reference: ACMMP::GetSupportPoints / DelaunayTriangulation / GetPriorPlaneParams
 // / GetDepthFromPlaneParam (ACMMP.cpp:868-958) and the raster + range check in
 // ProcessProblem (acmmp_definitions.cpp:332-374).
+// Split: support-point selection, triangle rasterisation, plane fit and the
+// per-pixel range check are CUDA kernels (prior_kernels.cu.inc); only the 2-D
+// Delaunay triangulation of the (<= P/25) support points runs on the host.
 #pragma once
 #include <stdint.h>
+
+#include <vector>
 
 #include "../../include/acmmp_b200.h"
 
 namespace acmmp {
 
-// prior4: W*H*4 floats (plane per pixel, only where mask > 0); mask: W*H labels
-// (triangle index + 1, 0 = none).
-void build_planar_prior_host(const acmmp_camera &cam, float depth_min, float depth_max, int W, int H,
-                             const float *costs, const float *depth, float *prior4, uint32_t *mask,
-                             int *num_support, int *num_triangles);
+// Delaunay triangulation of n integer points (x0,y0,x1,y1,...).  Appends
+// 6 ints per triangle (x,y of the three vertices) to `tris`; returns the count.
+int delaunay_triangulate(const int32_t *xy, int n, std::vector<int32_t> &tris);
 
 }  // namespace acmmp

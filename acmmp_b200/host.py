@@ -103,6 +103,14 @@ class ACMMP:
         _check(self._ctx, self._lib.acmmp_build_planar_prior(self._ctx, C.byref(ns), C.byref(nt)), "BuildPlanarPrior")
         return ns.value, nt.value
 
+    def GetPlanarPrior(self):
+        """prior planes (H,W,4) and triangle labels (H,W) as uploaded."""
+        h, w = self._shape()
+        pl = np.empty((h, w, 4), np.float32)
+        m = np.empty((h, w), np.uint32)
+        _check(self._ctx, self._lib.acmmp_get_planar_prior(self._ctx, L.fptr(pl), L.uptr(m)), "GetPlanarPrior")
+        return pl, m
+
     # ---- run ----------------------------------------------------------------------------
     def RunPatchMatch(self, seed=0):
         _check(self._ctx, self._lib.acmmp_run(self._ctx, int(seed)), "RunPatchMatch")
@@ -208,6 +216,19 @@ def resize_linear(image, new_w, new_h, device=0):
     out = np.empty((new_h, new_w), np.float32)
     _check(None, lib.acmmp_resize_linear(device, L.fptr(img), img.shape[1], img.shape[0], L.fptr(out), new_w, new_h), "resize_linear")
     return out
+
+
+def DelaunayTriangulation(points):
+    """points (n,2) int -> triangles (m,3,2) int (ACMMP.cpp:896-918); host only."""
+    lib = L.load()
+    pts = np.ascontiguousarray(points, np.int32).reshape(-1, 2)
+    cap = max(2 * len(pts), 1)
+    out = np.zeros((cap, 6), np.int32)
+    i32 = C.POINTER(C.c_int32)
+    nt = lib.acmmp_delaunay(pts.ctypes.data_as(i32), len(pts), out.ctypes.data_as(i32), cap)
+    if nt < 0:
+        raise L.AcmmpError(f"acmmp_delaunay failed ({nt})")
+    return out[:nt].reshape(-1, 3, 2)
 
 
 def rng_init_states(seed, w, h, device=0):

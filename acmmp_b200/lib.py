@@ -57,7 +57,7 @@ EXPORTS = [
     "acmmp_run_sweep", "acmmp_run_tail", "acmmp_get_result", "acmmp_get_maps",
     "acmmp_get_depth_device", "acmmp_get_state", "acmmp_set_state", "acmmp_width", "acmmp_height",
     "acmmp_sync", "acmmp_launch_count", "acmmp_last_timing", "acmmp_jbu_depth", "acmmp_resize_linear",
-    "acmmp_rng_init_states", "acmmp_measure_fp32_peak",
+    "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_get_planar_prior", "acmmp_delaunay",
 ]
 
 _lib = None
@@ -96,6 +96,8 @@ def load():
     lib.acmmp_set_seeded_planes.argtypes = [vp, fp]
     lib.acmmp_set_planar_prior.argtypes = [vp, fp, up]
     lib.acmmp_build_planar_prior.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.acmmp_get_planar_prior.argtypes = [vp, fp, up]
+    lib.acmmp_delaunay.argtypes = [C.POINTER(C.c_int32), C.c_int, C.POINTER(C.c_int32), C.c_int]
     lib.acmmp_run.argtypes = [vp, C.c_uint64]
     lib.acmmp_run_init.argtypes = [vp, C.c_uint64]
     lib.acmmp_run_sweep.argtypes = [vp, C.c_int, C.c_int]

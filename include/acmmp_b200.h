@@ -154,6 +154,16 @@ int acmmp_set_planar_prior(acmmp_ctx *ctx, const float *planes4,
  * acmmp_definitions.cpp:306-378).  Outputs are optional (may be NULL). */
 int acmmp_build_planar_prior(acmmp_ctx *ctx, int *num_support,
                              int *num_triangles);
+/* read back the per-pixel prior planes (4 f32) and triangle labels (u32) that
+ * the reference keeps in prior_planes_host / plane_masks_host
+ * (ACMMP.cpp:813-827).  NULL = skip. */
+int acmmp_get_planar_prior(acmmp_ctx *ctx, float *planes4, uint32_t *mask);
+/* 2-D Delaunay triangulation of n integer points (x,y pairs) = the host step of
+ * ACMMP::DelaunayTriangulation (ACMMP.cpp:896-918, cv::Subdiv2D there).  Writes
+ * up to `capacity` triangles (6 ints each: x,y of the 3 vertices); returns the
+ * triangle count (>= 0) or a negative status.  Pure host code: no device
+ * needed. */
+int acmmp_delaunay(const int32_t *xy, int n, int32_t *tris, int capacity);
 
 /* ---- run -------------------------------------------------------------------
  * ACMMP::RunPatchMatch (ACMMP.cu:1378-1456).  `seed` replaces the reference's
