@@ -57,7 +57,12 @@ struct LayeredImages {
 struct acmmp_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    // event quads (start, after init, after sweeps, after tail) of every acmmp_run since the
+    // last acmmp_timing_collect; the newest quad also serves acmmp_last_timing
+    std::vector<cudaEvent_t> evpool;
+    size_t ev_used = 0;
+    size_t last_quad = 0;
+    bool have_quad = false;
     std::string error;
     acmmp_params params;
     int compat = ACMMP_COMPAT_REF_SM100;
@@ -231,7 +236,6 @@ int acmmp_create(acmmp_ctx **out, int device) {
         delete ctx;
         return fail(nullptr, ACMMP_ERR_CUDA, "cannot create stream on device %d", device);
     }
-    for (auto &ev : ctx->ev) cudaEventCreate(&ev);
     *out = ctx;
     return 0;
 }
@@ -247,7 +251,7 @@ void acmmp_destroy(acmmp_ctx *ctx) {
                       &ctx->costs_snap, &ctx->seeded, &ctx->prior_planes, &ctx->plane_masks, &ctx->scaled_planes,
                       &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c, &ctx->tri_buf};
     for (auto *b : bufs) b->release();
-    for (auto &ev : ctx->ev)
+    for (auto &ev : ctx->evpool)
         if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -444,3 +448,4 @@ int acmmp_set_planar_prior(acmmp_ctx *ctx, const float *planes4, const uint32_t 
 }  // extern "C"
 
 #include "capi_run.cu.inc"
+#include "capi_scan.cu.inc"

@@ -243,3 +243,115 @@ def measure_fp32_peak(device=0):
     a, b = C.c_double(), C.c_double()
     _check(None, lib.acmmp_measure_fp32_peak(device, C.byref(a), C.byref(b)), "measure_fp32_peak")
     return a.value, b.value
+
+
+STAGE_PHOTO, STAGE_GEOM0, STAGE_GEOM1 = 0, 1, 2
+
+
+class Scan:
+    """The stage graph of the reference's main() (main_ACMMP.cpp:89-176) over a set of
+    views with all data resident on the device; `exchange` is called after every
+    stage with (device pointer, floats per rank segment) so that a multi-GPU caller
+    can all-gather the depth maps (no-op on one GPU)."""
+
+    def __init__(self, cams, pairs, device=0, rank=0, world=1, sequential_geom=False):
+        self._lib = L.load()
+        self._s = C.c_void_p()
+        n = len(cams)
+        cam_arr = (L.Camera * n)(*[c.copy() for c in cams])
+        offs = np.zeros(n + 1, np.int32)
+        for i, p in enumerate(pairs):
+            offs[i + 1] = offs[i] + len(p)
+        ids = np.ascontiguousarray([j for p in pairs for j in p], np.int32)
+        i32 = C.POINTER(C.c_int32)
+        rc = self._lib.acmmp_scan_create(C.byref(self._s), device, n, cam_arr, offs.ctypes.data_as(i32), ids.ctypes.data_as(i32))
+        if rc != 0:
+            raise L.AcmmpError(f"acmmp_scan_create failed ({rc}): {self._lib.acmmp_last_error(None).decode()}")
+        self.n, self.rank, self.world = n, rank, world
+        self._ck(self._lib.acmmp_scan_set_shard(self._s, rank, world), "set_shard")
+        self._ck(self._lib.acmmp_scan_set_sequential_geom(self._s, int(sequential_geom)), "set_sequential_geom")
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise L.AcmmpError(f"{what} failed ({rc}): {self._lib.acmmp_scan_last_error(self._s).decode()}")
+
+    def close(self):
+        if self._s:
+            self._lib.acmmp_scan_destroy(self._s)
+            self._s = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def owned(self):
+        return [v for v in range(self.n) if v % self.world == self.rank]
+
+    def set_image(self, view, gray, on_device=False):
+        """gray: float32 HxW numpy array (host, may be pinned) or an int device pointer."""
+        if on_device:
+            self._ck(self._lib.acmmp_scan_set_image(self._s, view, C.c_void_p(int(gray)), 1), "set_image")
+        else:
+            g = L.f32(gray)
+            self._ck(self._lib.acmmp_scan_set_image(self._s, view, C.c_void_p(g.ctypes.data), 0), "set_image")
+            self.sync()   # the host array may be released after this returns
+
+    def num_levels(self):
+        return self._lib.acmmp_scan_num_levels(self._s)
+
+    def begin_level(self, level):
+        self._ck(self._lib.acmmp_scan_begin_level(self._s, level), "begin_level")
+
+    def run_stage(self, stage, seed=0):
+        self._ck(self._lib.acmmp_scan_run_stage(self._s, stage, int(seed)), "run_stage")
+
+    def exchange_info(self):
+        ptr, stride, slots = C.c_void_p(), C.c_int64(), C.c_int()
+        self._ck(self._lib.acmmp_scan_exchange(self._s, C.byref(ptr), C.byref(stride), C.byref(slots)), "exchange")
+        return ptr.value, stride.value, slots.value
+
+    def view_size(self, view):
+        w, h = C.c_int(), C.c_int()
+        self._ck(self._lib.acmmp_scan_view_size(self._s, view, C.byref(w), C.byref(h)), "view_size")
+        return w.value, h.value
+
+    def get_view(self, view, want_normal=True, want_cost=True):
+        w, h = self.view_size(view)
+        d = np.empty((h, w), np.float32)
+        n = np.empty((h, w, 3), np.float32) if want_normal else None
+        c = np.empty((h, w), np.float32) if want_cost else None
+        self._ck(self._lib.acmmp_scan_get_view(self._s, view, L.fptr(d), L.fptr(n), L.fptr(c)), "get_view")
+        return d, n, c
+
+    def timing(self):
+        out, runs, launches = (C.c_double * 4)(), C.c_int(), C.c_uint64()
+        self._ck(self._lib.acmmp_scan_timing(self._s, C.byref(out), C.byref(runs), C.byref(launches)), "timing")
+        return {"init_ms": out[0], "sweeps_ms": out[1], "tail_ms": out[2], "total_ms": out[3], "runs": runs.value,
+                "launches": int(launches.value)}
+
+    def sync(self):
+        self._ck(self._lib.acmmp_scan_sync(self._s), "sync")
+
+    def reset(self):
+        self._ck(self._lib.acmmp_scan_reset(self._s), "reset")
+
+    def mark(self, i):
+        self._ck(self._lib.acmmp_scan_mark(self._s, i), "mark")
+
+    def elapsed_ms(self, i, j):
+        ms = C.c_float()
+        self._ck(self._lib.acmmp_scan_elapsed(self._s, i, j, C.byref(ms)), "elapsed")
+        return float(ms.value)
+
+    def run_all(self, seed=0, exchange=None, stages=(STAGE_PHOTO, STAGE_GEOM0, STAGE_GEOM1), levels=None):
+        """the full-ACMMP schedule: for every level, coarse to fine: photometric +
+        planar prior, geom-0, geom-1."""
+        nl = self.num_levels() if levels is None else levels
+        for level in range(nl):
+            self.begin_level(level)
+            for st in stages:
+                self.run_stage(st, seed)
+                if exchange is not None:
+                    exchange(*self.exchange_info())

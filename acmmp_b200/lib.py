@@ -57,7 +57,11 @@ EXPORTS = [
     "acmmp_run_sweep", "acmmp_run_tail", "acmmp_get_result", "acmmp_get_maps",
     "acmmp_get_depth_device", "acmmp_get_state", "acmmp_set_state", "acmmp_width", "acmmp_height",
     "acmmp_sync", "acmmp_launch_count", "acmmp_last_timing", "acmmp_jbu_depth", "acmmp_resize_linear",
-    "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_get_planar_prior", "acmmp_delaunay",
+    "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_get_planar_prior", "acmmp_delaunay", "acmmp_timing_collect",
+    "acmmp_scan_create", "acmmp_scan_destroy", "acmmp_scan_last_error", "acmmp_scan_set_image",
+    "acmmp_scan_set_shard", "acmmp_scan_set_sequential_geom", "acmmp_scan_num_levels", "acmmp_scan_begin_level",
+    "acmmp_scan_run_stage", "acmmp_scan_exchange", "acmmp_scan_view_size", "acmmp_scan_get_view",
+    "acmmp_scan_timing", "acmmp_scan_sync", "acmmp_scan_reset", "acmmp_scan_mark", "acmmp_scan_elapsed",
 ]
 
 _lib = None
@@ -113,10 +117,31 @@ def load():
     lib.acmmp_launch_count.argtypes = [vp]
     lib.acmmp_launch_count.restype = C.c_uint64
     lib.acmmp_last_timing.argtypes = [vp, C.POINTER(C.c_float * 4)]
+    lib.acmmp_timing_collect.argtypes = [vp, C.POINTER(C.c_double * 4), C.POINTER(C.c_int)]
     lib.acmmp_jbu_depth.argtypes = [C.c_int, fp, C.c_int, C.c_int, fp, C.c_int, C.c_int, fp]
     lib.acmmp_resize_linear.argtypes = [C.c_int, fp, C.c_int, C.c_int, fp, C.c_int, C.c_int]
     lib.acmmp_rng_init_states.argtypes = [C.c_int, C.c_uint64, C.c_int, C.c_int, up]
     lib.acmmp_measure_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    i32p = C.POINTER(C.c_int32)
+    lib.acmmp_scan_create.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.POINTER(Camera), i32p, i32p]
+    lib.acmmp_scan_destroy.argtypes = [vp]
+    lib.acmmp_scan_destroy.restype = None
+    lib.acmmp_scan_last_error.argtypes = [vp]
+    lib.acmmp_scan_last_error.restype = C.c_char_p
+    lib.acmmp_scan_set_image.argtypes = [vp, C.c_int, vp, C.c_int]
+    lib.acmmp_scan_set_shard.argtypes = [vp, C.c_int, C.c_int]
+    lib.acmmp_scan_set_sequential_geom.argtypes = [vp, C.c_int]
+    lib.acmmp_scan_num_levels.argtypes = [vp]
+    lib.acmmp_scan_begin_level.argtypes = [vp, C.c_int]
+    lib.acmmp_scan_run_stage.argtypes = [vp, C.c_int, C.c_uint64]
+    lib.acmmp_scan_exchange.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_int64), C.POINTER(C.c_int)]
+    lib.acmmp_scan_view_size.argtypes = [vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.acmmp_scan_get_view.argtypes = [vp, C.c_int, fp, fp, fp]
+    lib.acmmp_scan_timing.argtypes = [vp, C.POINTER(C.c_double * 4), C.POINTER(C.c_int), C.POINTER(C.c_uint64)]
+    lib.acmmp_scan_sync.argtypes = [vp]
+    lib.acmmp_scan_reset.argtypes = [vp]
+    lib.acmmp_scan_mark.argtypes = [vp, C.c_int]
+    lib.acmmp_scan_elapsed.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float)]
     _lib = lib
     return lib
 

@@ -203,6 +203,9 @@ uint64_t acmmp_launch_count(const acmmp_ctx *ctx);
 /* device time of the last acmmp_run in ms, split per kernel family:
  * out[0]=init out[1]=sweeps out[2]=tail out[3]=total (CUDA events). */
 int acmmp_last_timing(acmmp_ctx *ctx, float out[4]);
+/* sums of the same four device times (ms) over every acmmp_run since the last
+ * collect (synchronises the context's stream); *runs = how many. */
+int acmmp_timing_collect(acmmp_ctx *ctx, double out_ms[4], int *runs);
 
 /* ---- JBU ---------------------------------------------------------------------
  * RunJBU / JBU::CudaRun / JBU_cu (ACMMP.cpp:1022-1087, ACMMP.cu:1458-1549):
@@ -229,6 +232,71 @@ int acmmp_rng_init_states(int device, uint64_t seed, int w, int h,
 /* ---- micro-benchmarks used by bench.py for the roofline denominators --------
  * measured FP32 FMA throughput (TFLOP/s), MUFU rate (Gop/s). */
 int acmmp_measure_fp32_peak(int device, double *tflops, double *mufu_gops);
+
+/* ==== whole-scan schedule ======================================================
+ * The stage graph of main() (/root/reference/src/main_ACMMP.cpp:89-176) over a
+ * set of views, with everything resident in device memory: image pyramids of
+ * ALL views, and the depth / normal / cost maps the reference hands from stage
+ * to stage through <out>/2333_%08d/{depths,depths_geom,normals,costs}.dmb
+ * (acmmp_definitions.cpp:392-401, ACMMP.cpp:608-635,710-808).
+ *
+ * Sharding: rank r of `world` owns the views v with v % world == r and runs
+ * ProcessProblem (acmmp_definitions.cpp:245-403) for them only.  Only depth
+ * maps cross views (ACMMP.cpp:608-635); after every stage the caller
+ * all-gathers the exchange buffer (acmmp_scan_exchange) across ranks - the
+ * library itself never communicates.
+ *
+ * levels: ComputeMultiScaleSettings (acmmp_definitions.cpp:207-243); level 0 is
+ * the coarsest.  Stages per level, in order:
+ *   ACMMP_STAGE_PHOTO  geom=F planar=T (hierarchy=T on levels > 0, after the JBU
+ *                      upsample of the previous level's depths_geom)
+ *   ACMMP_STAGE_GEOM0  geom=T multi=F      ACMMP_STAGE_GEOM1  geom=T multi=T
+ */
+typedef struct acmmp_scan acmmp_scan;
+enum { ACMMP_STAGE_PHOTO = 0, ACMMP_STAGE_GEOM0 = 1, ACMMP_STAGE_GEOM1 = 2 };
+
+/* pairs: pair.txt as CSR (GenerateSampleList, acmmp_definitions.cpp:179-205;
+ * sources with score <= 0 already dropped); ids are view indices 0..n-1.
+ * cams: full-resolution cameras as read by ReadCamera (ACMMP.cpp:154-179) with
+ * width/height = the image size. */
+int acmmp_scan_create(acmmp_scan **out, int device, int n_views, const acmmp_camera *cams,
+                      const int32_t *pair_offsets, const int32_t *pair_ids);
+void acmmp_scan_destroy(acmmp_scan *s);
+const char *acmmp_scan_last_error(const acmmp_scan *s);
+/* full-resolution grey image of one view as float (imread GRAYSCALE +
+ * convertTo CV_32F, ACMMP.cpp:539-541); host or device pointer. */
+int acmmp_scan_set_image(acmmp_scan *s, int view, const float *gray, int on_device);
+int acmmp_scan_set_shard(acmmp_scan *s, int rank, int world);
+/* 0 = Jacobi (default; geom-1 reads the geom-0 maps of all views), 1 = the
+ * reference's in-place order dependence (geom-1 reads what earlier views of the
+ * same loop already wrote; only meaningful with world == 1). */
+int acmmp_scan_set_sequential_geom(acmmp_scan *s, int on);
+int acmmp_scan_num_levels(const acmmp_scan *s);
+/* builds the image pyramid level (InputInitialization's resize,
+ * ACMMP.cpp:566-598) for all views, and for level > 0 runs
+ * JointBilateralUpsampling (acmmp_definitions.cpp:405-440) for the owned views. */
+int acmmp_scan_begin_level(acmmp_scan *s, int level);
+int acmmp_scan_run_stage(acmmp_scan *s, int stage, uint64_t seed);
+/* the depth maps written by the last stage / begin_level: one device buffer of
+ * world * slots * stride floats, rank r's segment = [r * slots * stride,
+ * (r+1) * slots * stride); view v lives in segment v % world, slot v / world. */
+int acmmp_scan_exchange(acmmp_scan *s, float **d_buffer, int64_t *stride, int *slots);
+/* size of view v at the current level */
+int acmmp_scan_view_size(const acmmp_scan *s, int view, int *w, int *h);
+/* current maps of an owned view (.dmb payloads; depth = the last written depth
+ * map); host pointers, any may be NULL. */
+int acmmp_scan_get_view(acmmp_scan *s, int view, float *depth, float *normal3, float *cost);
+/* device time spent in kernels, summed over all runs since the last call:
+ * out_ms[0..3] = init, sweeps, tail, total; *runs = RunPatchMatch count;
+ * *launches = kernel launches so far. */
+int acmmp_scan_timing(acmmp_scan *s, double out_ms[4], int *runs, uint64_t *launches);
+int acmmp_scan_sync(acmmp_scan *s);
+/* start the schedule over (level 0 next) keeping images and buffers */
+int acmmp_scan_reset(acmmp_scan *s);
+/* CUDA events on the scan's stream: record mark i (0..7); elapsed ms between
+ * two recorded marks (waits for mark j). */
+int acmmp_scan_mark(acmmp_scan *s, int i);
+int acmmp_scan_elapsed(acmmp_scan *s, int i, int j, float *ms);
 
 #ifdef __cplusplus
 }
