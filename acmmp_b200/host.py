@@ -289,14 +289,16 @@ class Scan:
     def owned(self):
         return [v for v in range(self.n) if v % self.world == self.rank]
 
-    def set_image(self, view, gray, on_device=False):
-        """gray: float32 HxW numpy array (host, may be pinned) or an int device pointer."""
+    def set_image(self, view, gray, on_device=False, sync=True):
+        """gray: float32 HxW numpy array (host, may be pinned) or an int device pointer.
+        sync=False: the caller keeps the host array alive until the next sync()."""
         if on_device:
             self._ck(self._lib.acmmp_scan_set_image(self._s, view, C.c_void_p(int(gray)), 1), "set_image")
         else:
             g = L.f32(gray)
             self._ck(self._lib.acmmp_scan_set_image(self._s, view, C.c_void_p(g.ctypes.data), 0), "set_image")
-            self.sync()   # the host array may be released after this returns
+            if sync:
+                self.sync()   # the host array may be released after this returns
 
     def num_levels(self):
         return self._lib.acmmp_scan_num_levels(self._s)
@@ -317,11 +319,14 @@ class Scan:
         self._ck(self._lib.acmmp_scan_view_size(self._s, view, C.byref(w), C.byref(h)), "view_size")
         return w.value, h.value
 
-    def get_view(self, view, want_normal=True, want_cost=True):
+    def get_view(self, view, want_normal=True, want_cost=True, out=None):
         w, h = self.view_size(view)
-        d = np.empty((h, w), np.float32)
-        n = np.empty((h, w, 3), np.float32) if want_normal else None
-        c = np.empty((h, w), np.float32) if want_cost else None
+        if out is not None:
+            d, n, c = out
+        else:
+            d = np.empty((h, w), np.float32)
+            n = np.empty((h, w, 3), np.float32) if want_normal else None
+            c = np.empty((h, w), np.float32) if want_cost else None
         self._ck(self._lib.acmmp_scan_get_view(self._s, view, L.fptr(d), L.fptr(n), L.fptr(c)), "get_view")
         return d, n, c
 

@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""bench.py - views/s of full ACMMP (multi-scale + planar prior + geometric
+consistency) on a synthetic DTU-shaped scan, 1..8 B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One "step" = the whole schedule of the reference's main() (main_ACMMP.cpp:89-176)
+over the 49-view scan, sharded by view across the N ranks (strong scaling: the
+scan is fixed, depth maps are all-gathered over NCCL after every stage).
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for the definitions.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+FLOP_PER_NCC = 1538.0          # 36 x 38 + 170
+HYP_PER_RUN = 29               # 1 (init) + 2 x 14; 30 for the hierarchy (upsample-init) run
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--views", type=int, default=49)
+    ap.add_argument("--width", type=int, default=1600)
+    ap.add_argument("--height", type=int, default=1200)
+    ap.add_argument("--nsrc", type=int, default=10)
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-views", type=int, default=4, help="views per step of the reference arm (bounded sample)")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop, self.th = index, [], threading.Event(), None
+
+    def _loop(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.2)
+
+    def __enter__(self):
+        self.th = threading.Thread(target=self._loop, daemon=True)
+        self.th.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.th.join(timeout=6)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def dist_setup(args):
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29512")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+    return rank, local, world, dist
+
+
+def make_scan_inputs(args, device):
+    """Synthetic DTU-shaped scan: 49 cameras on a 7x7 cap, f = 2892 px,
+    depth range as in DTU cam files, 10 nearest views as sources; rendered on the
+    device, integer-valued grey images like decoded JPEGs."""
+    from acmmp_b200.scene import make_scene
+    sc = make_scene(args.views, args.width, args.height, args.nsrc, seed=args.seed, device=device, as_numpy=False)
+    return sc
+
+
+class DevPtr:
+    """lets torch alias a raw device pointer (CUDA array interface)."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+def hyp_evals_per_view(scan_sizes):
+    """(w, h) per level -> hypothesis evaluations of one view of full ACMMP: 4 runs
+    per level, 29 per pixel per run, 30 for the hierarchy run."""
+    total = 0
+    for lvl, (w, h) in enumerate(scan_sizes):
+        total += w * h * (4 * HYP_PER_RUN + (1 if lvl > 0 else 0))
+    return total
+
+
+def run_ours(args):
+    import torch
+    from acmmp_b200 import host
+    rank, local, world, dist = dist_setup(args)
+    dev = torch.device("cuda", local)
+    sc = make_scan_inputs(args, dev)
+    n = args.views
+    imgs_dev = [im.contiguous().float() for im in sc["images"]]
+    imgs_host = [torch.empty(im.shape, dtype=torch.float32).pin_memory() for im in imgs_dev]
+    for h_, d_ in zip(imgs_host, imgs_dev):
+        h_.copy_(d_)
+    torch.cuda.synchronize()
+    imgs_np = [t.numpy() for t in imgs_host]
+    scan = host.Scan(sc["cams"], sc["pairs"], device=local, rank=rank, world=world)
+    owned = scan.owned()
+    H, W = args.height, args.width
+    outs = {v: (torch.empty((H, W), dtype=torch.float32).pin_memory().numpy(),
+                torch.empty((H, W, 3), dtype=torch.float32).pin_memory().numpy(),
+                torch.empty((H, W), dtype=torch.float32).pin_memory().numpy()) for v in owned}
+    n_exchanges = [0]
+
+    def exchange(ptr, stride, slots):
+        if world == 1:
+            return
+        seg = int(stride) * int(slots)
+        scan.sync()
+        t = torch.as_tensor(DevPtr(ptr, seg * world), device=dev)
+        mine = t[rank * seg:(rank + 1) * seg].clone()
+        dist.all_gather_into_tensor(t, mine)
+        torch.cuda.current_stream().synchronize()
+        n_exchanges[0] += 1
+
+    def step(e2e):
+        scan.reset()
+        for v in range(n):
+            if e2e:
+                scan.set_image(v, imgs_np[v], sync=False)
+            else:
+                scan.set_image(v, imgs_dev[v].data_ptr(), on_device=True)
+        scan.run_all(seed=1234, exchange=exchange)
+        if e2e:
+            for v in owned:
+                scan.get_view(v, out=outs[v])
+
+    def barrier():
+        scan.sync()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+
+    def timed(k, e2e):
+        barrier()
+        scan.mark(0)
+        for _ in range(k):
+            step(e2e)
+        scan.mark(1)
+        barrier()
+        ms = torch.tensor([scan.elapsed_ms(0, 1)], device=dev, dtype=torch.float64)
+        if dist is not None:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(args.warmup):
+        step(False)
+    barrier()
+    scan.timing()                      # clear the kernel-time log
+    l0 = scan.timing()["launches"]
+    with ClockSampler(local) as clocks:
+        ms_dev = timed(args.steps, False)
+    tm = scan.timing()
+    launches = tm["launches"] - l0
+    step(True)                          # e2e warm-up (pinned staging paths)
+    ms_e2e = timed(args.steps, True)
+    sizes = []
+    scan.reset()
+    for lvl in range(scan.num_levels()):
+        scan.begin_level(lvl)
+        sizes.append(scan.view_size(0))
+    scan.sync()
+    fp32_tflops, mufu_gops = host.measure_fp32_peak(local)
+    hpv = hyp_evals_per_view(sizes)
+    views_per_s = n * args.steps / (ms_dev * 1e-3)
+    e2e_views_per_s = n * args.steps / (ms_e2e * 1e-3)
+    # dominant kernel: sweep_kernel.  algorithmic NCC evaluations of rank 0's runs in the
+    # timed region: per run P * 28 hypotheses * nsrc views
+    ncc_sweeps = sum(4 * w * h * 28 * args.nsrc for (w, h) in sizes) * len(owned) * args.steps
+    achieved = ncc_sweeps * FLOP_PER_NCC / (tm["sweeps_ms"] * 1e-3) / 1e12
+    h2d = sum(int(np.prod(im.shape)) * 4 for im in imgs_np)
+    d2h = len(owned) * H * W * 5 * 4
+    line = {
+        "metric": "views/s, DTU-shape 1600x1200 49-view full ACMMP (multi-scale + planar prior + geometric consistency)",
+        "value": views_per_s, "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"configs[2]: DTU-shape {W}x{H} x {n} views, {args.nsrc} sources, full ACMMP "
+                               f"({len(sizes)} scales x (photometric+planar prior, geom x2))",
+                   "levels": [list(s) for s in sizes], "sharding": f"view % {world}", "exchange": "nccl all_gather of depth maps per stage",
+                   "l2": "inputs (49 x 7.7 MB images + per-view state) exceed the 126 MB L2; no explicit flush",
+                   "hyp_evals_per_view": hpv},
+        "mpix_hyp_per_s": views_per_s * hpv / 1e6,
+        "e2e": {"value": e2e_views_per_s, "unit": "views/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e / args.steps, "mpix_hyp_per_s": e2e_views_per_s * hpv / 1e6},
+        "gpu_launches": int(launches),
+        "kernel_ms_per_step": {k: tm[k] / args.steps for k in ("init_ms", "sweeps_ms", "tail_ms", "total_ms")},
+        "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_tflops, "unit": "TFLOP/s", "frac": achieved / fp32_tflops,
+                     "traffic": None, "kernel": "sweep_kernel",
+                     "note": "FP32/texture-bound path (no HBM or tensor bound applies): achieved = algorithmic NCC evaluations x 1538 flop / "
+                             "sweep_kernel time (CUDA events on the launching stream); peak = FP32 FMA rate measured live by fp32_peak_kernel "
+                             "(MEASURED_PEAKS.json has no FP32 figure)", "mufu_gops_measured": mufu_gops},
+        "clocks": clocks.summary(),
+        "exchanges_per_step": n_exchanges[0] // max(1, (args.warmup + 2 * args.steps + 1)),
+    }
+    if rank == 0 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args, sc, hpv)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    scan.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(args, sc, hyp_per_view):
+    """The CPU port of the path (oracle/*.c, single thread) on a bounded sample of the
+    same workload: one reference view of the scan with its sources at full
+    resolution, random init on a (inner + 24 px margin) window, then the four
+    half-sweeps on the inner window."""
+    import oraclebind as ob
+    ref = args.views // 2
+    ids = [ref] + sc["pairs"][ref]
+    images = [sc["images"][i].cpu().numpy() for i in ids]
+    cams = [sc["cams"][i] for i in ids]
+    H, W = images[0].shape
+    iw, ih, m = 96, 64, 24
+    x0, y0 = W // 2 - iw // 2, H // 2 - ih // 2
+    pr = ob.Problem(images, cams)
+    pr.rng_init(1234)
+    t0 = time.time()
+    pr.init(ob.INIT_RANDOM, (x0 - m, y0 - m, x0 + iw + m, y0 + ih + m))
+    for it in range(2):
+        for color in range(2):
+            pr.sweep(it, color, (x0, y0, x0 + iw, y0 + ih))
+    dt = time.time() - t0
+    hyp = (iw + 2 * m) * (ih + 2 * m) * 1 + iw * ih * 28
+    return {"value": hyp / dt / hyp_per_view, "unit": "views/s", "cores": 1, "kind": "port",
+            "mpix_hyp_per_s": hyp / dt / 1e6,
+            "sample": f"view {ref} + {len(ids) - 1} sources at {W}x{H}: random init on a {iw + 2 * m}x{ih + 2 * m} window + 2x(black,red) sweeps "
+                      f"on the inner {iw}x{ih} ({hyp} hypothesis evaluations, {dt:.1f} s), scaled by {hyp_per_view} evaluations per view",
+            "note": "the reference has no CPU PatchMatch; this is the oracle restatement (exact libm, no SIMD)"}
+
+
+def run_reference(args):
+    """Baseline arm: the reference's own CUDA kernels (oracle/_ref, compiled from
+    /root/reference/src/ACMMP.cu for sm_100 with the reference's flags) in the
+    reference's own per-view / per-stage flow (oracle/ref_pipeline.py), 1 GPU - the
+    reference has no multi-GPU mode and no CPU PatchMatch.  Each step = a bounded
+    sample of the scan: --ref-views reference views go through the whole schedule
+    with all their sources; views outside the sample contribute ground-truth depth
+    maps to the geometric-consistency stages, so the work per view is that of the
+    full scan."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refbind
+    if not refbind.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libacmmp_ref.so was not built (needs /root/reference at build time)"}))
+        return
+    import cv2
+    import ref_pipeline
+    torch.cuda.set_device(0)
+    sc = make_scan_inputs(args, torch.device("cuda", 0))
+    images = [im.cpu().numpy() for im in sc["images"]]
+    gts = [d.cpu().numpy() for d in sc["depths"]]
+    n = args.views
+    centre = n // 2
+    sample = sorted(set([centre] + sc["pairs"][centre][:max(0, args.ref_views - 1)]))
+    rs = ref_pipeline.RefScan(images, sc["cams"], sc["pairs"], 0)
+
+    def external(i, w, h):
+        g = gts[i]
+        return g if g.shape == (h, w) else cv2.resize(g, (w, h), interpolation=cv2.INTER_NEAREST)
+
+    sizes = []
+    mis, nds, mx = ref_pipeline.multi_scale_settings(sc["cams"])
+    for lvl in range(mx + 1):
+        w, h, _ = ref_pipeline.level_geometry(sc["cams"][0], int(mis[0] / 2 ** (nds[0] - lvl)))
+        sizes.append((w, h))
+    hpv = hyp_evals_per_view(sizes)
+    for _ in range(min(args.warmup, 1)):       # one warm-up pass is enough for a synchronous flow
+        rs.run_all(1234, sample, external)
+    torch.cuda.synchronize()
+    rs.kernel_ms, rs.prior_s, rs.runs = 0.0, 0.0, 0
+    with ClockSampler(0) as clocks:
+        t0 = time.time()
+        for _ in range(args.steps):
+            rs.run_all(1234, sample, external)
+        torch.cuda.synchronize()
+        dt = time.time() - t0
+    v = len(sample) * args.steps / dt
+    H, W = args.height, args.width
+    line = {
+        "impl": "reference",
+        "metric": "views/s, DTU-shape 1600x1200 49-view full ACMMP (multi-scale + planar prior + geometric consistency)",
+        "value": v, "unit": "views/s", "n_gpus": 1, "steps": args.steps, "warmup": min(args.warmup, 1),
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"configs[2]: DTU-shape {W}x{H} x {n} views, {args.nsrc} sources, full ACMMP", "levels": [list(s) for s in sizes],
+                   "sample_views": sample, "hyp_evals_per_view": hpv,
+                   "what": "reference ACMMP.cu kernels (sm_100, -O3 --use_fast_math --maxrregcount=128) in the reference's per-view/"
+                           "per-stage flow; JPEG decode, .dmb disk I/O and imshow left out (in its favour); wall clock incl. its "
+                           "uploads, syncs, D2H and CPU planar prior"},
+        "mpix_hyp_per_s": v * hpv / 1e6,
+        "kernel_only": {"views_per_s": len(sample) * args.steps / (rs.kernel_ms * 1e-3), "kernel_ms": rs.kernel_ms, "runs": rs.runs},
+        "cpu_prior_s_per_view": rs.prior_s / (len(sample) * args.steps),
+        "cpu_baseline": {"value": v, "unit": "views/s", "cores": 1, "kind": "reference",
+                         "sample": f"{len(sample)} of {n} views per step (view {centre} and its nearest sources), all stages; "
+                                   "device = 1 B200 for the reference's CUDA kernels, 1 host thread for its CPU steps"},
+        "e2e": {"value": v, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "clocks": clocks.summary(),
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

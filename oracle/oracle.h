@@ -90,6 +90,11 @@ void orc_run(orc_problem *p, int mode, int iterations);
 int orc_jbu_depth(const float *image, int w, int h, const float *depth, int sw, int sh, float *out);
 void orc_resize_linear(const float *src, int sw, int sh, float *dst, int dw, int dh);
 
+/* planar prior around the triangulation (ACMMP.cpp:868-958, acmmp_definitions.cpp:332-374) */
+int orc_support_points(const float *costs, int W, int H, int32_t *xy /* 2 * ceil(W/5)*ceil(H/5) */);
+void orc_prior_from_triangles(const orc_camera *cam, const float *depth, int W, int H, const int32_t *tris, int ntri,
+                              float depth_min, float depth_max, float *tri_planes, float *prior4, uint32_t *mask);
+
 /* fusion (RunFusion, acmmp_definitions.cpp:828-1043); returns number of points.
  * pair_offsets: n+1 prefix offsets into pair_ids (source ids as indices).
  * points: capacity*9 floats (x,y,z,nx,ny,nz,c0,c1,c2) or NULL to count only. */

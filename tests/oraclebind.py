@@ -84,6 +84,10 @@ def load():
                                C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_int), C.POINTER(C.c_int),
                                C.c_float, C.c_int, fp, C.c_long]
     lib.orc_fusion.restype = C.c_long
+    i32p = C.POINTER(C.c_int32)
+    lib.orc_support_points.argtypes = [fp, C.c_int, C.c_int, i32p]
+    lib.orc_prior_from_triangles.argtypes = [C.POINTER(OrcCamera), fp, C.c_int, C.c_int, i32p, C.c_int, C.c_float, C.c_float, fp, fp, up]
+    lib.orc_prior_from_triangles.restype = None
     _lib = lib
     return lib
 
@@ -278,3 +282,24 @@ def fusion(cams, depths, normals, pairs, consistency_scalar=0.3, con_num_thresh=
     cnt = load().orc_fusion(n, cam_arr, dp, npz, cp, offs.ctypes.data_as(C.POINTER(C.c_int)),
                             ids.ctypes.data_as(C.POINTER(C.c_int)), consistency_scalar, con_num_thresh, _fp(pts), cap)
     return (int(cnt), pts[:cnt]) if want_points else int(cnt)
+
+
+def support_points(costs):
+    c = _f32(costs)
+    h, w = c.shape
+    xy = np.zeros((((w + 4) // 5) * ((h + 4) // 5), 2), np.int32)
+    n = load().orc_support_points(_fp(c), w, h, xy.ctypes.data_as(C.POINTER(C.c_int32)))
+    return xy[:n]
+
+
+def prior_from_triangles(cam, depth, tris, depth_min, depth_max):
+    d = _f32(depth)
+    h, w = d.shape
+    t = np.ascontiguousarray(tris, np.int32).reshape(-1, 6)
+    tri_planes = np.zeros((max(len(t), 1), 4), np.float32)
+    prior = np.zeros((h, w, 4), np.float32)
+    mask = np.zeros((h, w), np.uint32)
+    oc = to_orc_camera(cam)
+    load().orc_prior_from_triangles(C.byref(oc), _fp(d), w, h, t.ctypes.data_as(C.POINTER(C.c_int32)), len(t),
+                                    float(depth_min), float(depth_max), _fp(tri_planes), _fp(prior), _up(mask))
+    return prior, mask, tri_planes[:len(t)]

@@ -113,6 +113,13 @@ class RefACMMP:
         self._ck(self.lib.ref_get_state(self.ctx, L.fptr(planes), L.fptr(costs), L.uptr(sel), L.uptr(rng), L.fptr(pre)), "ref_get_state")
         return planes, costs, sel, rng, pre
 
+    def get_result(self):
+        """planes + costs only = the D2H of ACMMP::RunPatchMatch (ACMMP.cu:1453-1455)."""
+        planes = np.empty((self.h, self.w, 4), np.float32)
+        costs = np.empty((self.h, self.w), np.float32)
+        self._ck(self.lib.ref_get_state(self.ctx, L.fptr(planes), L.fptr(costs), None, None, None), "ref_get_state")
+        return planes, costs
+
     def run_init(self, seed):
         self._ck(self.lib.ref_run_init(self.ctx, seed), "ref_run_init")
 
