@@ -1,0 +1,177 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Everything goes through
+the C ABI (acmmp_b200.host -> libacmmp_b200.so).
+
+Three checkers:
+ * golden vectors captured from the REFERENCE's own kernels (tests/golden/ref_golden.npz):
+   the deterministic, race-free pieces must match bit for bit;
+ * the reference's kernels run live (oracle/_ref, when built) for step-exact half
+   sweeps from identical state;
+ * the CPU oracle (oracle/*.c) on fresh seeded inputs, within the stated tolerances.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import golden_util as gu
+import oraclebind as ob
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+if not torch.cuda.is_available():
+    pytest.skip("no CUDA device", allow_module_level=True)
+
+from acmmp_b200 import host, lib as L  # noqa: E402
+from acmmp_b200.scene import make_scene  # noqa: E402
+import refbind  # noqa: E402
+
+HAVE_REF = refbind.available()
+
+
+def interior(h, w, b):
+    m = np.zeros((h, w), bool)
+    m[b:h - b, b:w - b] = True
+    return m
+
+
+def color_mask(h, w, color):
+    yy, xx = np.mgrid[0:h, 0:w]
+    return ((xx + yy) & 1) == color
+
+
+# ---- golden vectors of the reference kernels ------------------------------------------
+
+def test_rng_states_bit_exact_vs_reference():
+    g, images, cams = gu.load()
+    h, w = images[0].shape
+    mine = host.rng_init_states(int(g["seed"][0]), w, h)
+    assert (mine == g["rng_after_seeded_init"]).all()
+
+
+@pytest.mark.parametrize("tag", ["p0", "p1", "p2"])
+def test_fixed_hypothesis_cost_and_view_masks_bit_exact_vs_reference(tag):
+    """north_star: per-pixel NCC within 1e-4, view-selection masks bit-exact, on
+    the fixed-hypothesis (`seeded`) initialisation."""
+    g, images, cams = gu.load()
+    m = host.ACMMP(0)
+    m.InputInitialization(images, cams)
+    m.SetPlanarPrior(g["planes_" + tag])
+    m.run_init(int(g["seed"][0]))
+    planes, cost, sel, _ = m.get_state(with_rng=False)
+    assert np.abs(cost - g["seeded_cost_" + tag]).max() <= 1e-4
+    assert (gu.bits(cost) == gu.bits(g["seeded_cost_" + tag])).all()
+    assert (sel == g["seeded_sel_" + tag]).all()
+    m.close()
+
+
+def test_random_init_bit_exact_vs_reference():
+    g, images, cams = gu.load()
+    m = host.ACMMP(0)
+    m.InputInitialization(images, cams)
+    m.run_init(int(g["seed"][0]))
+    planes, cost, sel, rng = m.get_state()
+    assert (gu.bits(planes) == gu.bits(g["rinit_planes"])).all()
+    assert (gu.bits(cost) == gu.bits(g["rinit_costs"])).all()
+    assert (sel == g["rinit_sel"]).all()
+    assert (rng == g["rinit_rng"]).all()
+    m.close()
+
+
+def test_first_half_sweep_vs_reference_golden():
+    """one black half-sweep from the (bit-identical) random init.  The reference's
+    same-colour reads race; the product serves them from a
+    snapshot, so a small fraction of pixels legitimately differs."""
+    g, images, cams = gu.load()
+    h, w = images[0].shape
+    m = host.ACMMP(0)
+    m.InputInitialization(images, cams)
+    m.run_init(int(g["seed"][0]))
+    m.run_sweep(0, 0)
+    planes, cost, sel, rng = m.get_state()
+    inner = interior(h, w, 4) & color_mask(h, w, 0)
+    same = (gu.bits(planes) == gu.bits(g["sweep00_planes"])).all(-1)
+    assert same[inner].mean() >= 0.985, same[inner].mean()
+    assert (rng == g["sweep00_rng"]).all(-1)[inner].mean() >= 0.999      # identical draw counts
+    other = color_mask(h, w, 1)
+    assert (gu.bits(planes) == gu.bits(g["rinit_planes"])).all(-1)[other].all()   # red pixels untouched
+    m.close()
+
+
+def test_full_run_vs_reference_golden():
+    g, images, cams = gu.load()
+    m = host.ACMMP(0)
+    m.InputInitialization(images, cams)
+    m.RunPatchMatch(int(g["seed"][0]))
+    planes = m.GetPlaneHypotheses()
+    inner = (slice(8, -8), slice(8, -8))
+    dk, nk = gu.depth_normal_ok(planes, g["final_planes"])
+    dk_ref, nk_ref = gu.depth_normal_ok(g["final_planes_rerun"], g["final_planes"])
+    # On this 96 x 72 image 8 % of the pixels are within 3 px of the border, where an arm
+    # of the checkerboard does not exist, the reference's arg-min picks that arm (its
+    # cost row is zero-filled, ACMMP.cu:805) and then stores the uninitialised
+    # plane_hypotheses_now (stack garbage: NaNs, (0,0,2,2) ...; tools/diag_sweep.py).  The
+    # product keeps the current plane there.  Garbage seeds spread through the far arms
+    # (23 px), so on an image this small a few per cent of the interior differs too.
+    assert dk[inner].mean() >= 0.93 * dk_ref[inner].mean(), (dk[inner].mean(), dk_ref[inner].mean())
+    gt = g["gt_depths"][0]
+    acc = (np.abs(planes[..., 3] - gt) / gt < 0.01)[inner].mean()
+    acc_ref = (np.abs(g["final_planes"][..., 3] - gt) / gt < 0.01)[inner].mean()
+    assert acc >= acc_ref - 0.01
+    m.close()
+
+
+def test_jbu_bit_exact_vs_reference():
+    g, images, cams = gu.load()
+    out = host.RunJBU(images[0], g["jbu_in_depth"])
+    assert (gu.bits(out) == gu.bits(g["jbu_out"])).all()
+    assert host.RunJBU(images[0], np.ones_like(images[0])) is None     # scale 1: the reference's early-out
+
+
+# ---- CPU oracle on fresh inputs ------------------------------------------------------------
+
+def test_initial_cost_vs_cpu_oracle():
+    sc = make_scene(5, 128, 96, 4, seed=3)
+    ids = [1] + sc["pairs"][1]
+    images = [sc["images"][i] for i in ids]
+    cams = [sc["cams"][i] for i in ids]
+    gt = sc["depths"][1]
+    planes = np.zeros(gt.shape + (4,), np.float32)
+    planes[..., 2] = -1.0
+    planes[..., 3] = gt * (1 + 0.01 * np.random.default_rng(0).standard_normal(gt.shape).astype(np.float32))
+    m = host.ACMMP(0)
+    m.InputInitialization(images, cams)
+    m.SetPlanarPrior(planes)
+    m.run_init(7)
+    _, cost, sel, _ = m.get_state(with_rng=False)
+    orc = ob.Problem(images, cams)
+    orc.set_seeded(planes)
+    orc.init(ob.INIT_SEEDED)
+    d = np.abs(cost - orc.costs)
+    assert d.mean() <= 1e-4 and (d <= 1e-4).mean() >= 0.9 and d.max() <= 1e-2
+    assert (sel == orc.sel).mean() >= 0.95
+    m.close()
+
+
+def test_tail_and_resize_vs_cpu_oracle():
+    rs = np.random.default_rng(4)
+    img = (rs.random((121, 161)) * 255).astype(np.float32)
+    assert np.abs(host.resize_linear(img, 80, 60) - ob.resize_linear(img, 80, 60)).max() <= 1e-3
+    sc = make_scene(3, 96, 72, 2, seed=5)
+    ids = [0] + sc["pairs"][0]
+    images = [sc["images"][i] for i in ids]
+    cams = [sc["cams"][i] for i in ids]
+    m = host.ACMMP(0)
+    m.InputInitialization(images, cams)
+    m.run_init(11)
+    planes, cost, sel, rng = m.get_state()
+    m.run_tail()
+    after = m.get_state()[0]
+    orc = ob.Problem(images, cams)
+    orc.set_state(planes, cost, sel, rng)
+    orc.tail()
+    ok = np.isfinite(orc.planes[..., 3]) & np.isfinite(after[..., 3])
+    assert np.abs(after[..., :3] - orc.planes[..., :3])[ok].max() <= 1e-5
+    rel = np.abs(after[..., 3] - orc.planes[..., 3])[ok] / np.maximum(np.abs(orc.planes[..., 3][ok]), 1e-6)
+    assert (rel <= 1e-5).mean() >= 0.999
+    m.close()
