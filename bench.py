@@ -122,7 +122,7 @@ def hyp_evals_per_view(scan_sizes):
 
 def run_ours(args):
     import torch
-    from acmmp_b200 import host
+    from acmmp_b200 import host, sharding
     rank, local, world, dist = dist_setup(args)
     dev = torch.device("cuda", local)
     sc = make_scan_inputs(args, dev)
@@ -147,8 +147,7 @@ def run_ours(args):
         seg = int(stride) * int(slots)
         scan.sync()
         t = torch.as_tensor(DevPtr(ptr, seg * world), device=dev)
-        mine = t[rank * seg:(rank + 1) * seg].clone()
-        dist.all_gather_into_tensor(t, mine)
+        sharding.all_gather_segments(t, rank, world, dist)
         torch.cuda.current_stream().synchronize()
         n_exchanges[0] += 1
 
