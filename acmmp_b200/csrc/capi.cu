@@ -10,6 +10,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <chrono>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -44,6 +45,27 @@ struct DevBuf {
     template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+// page-locked host staging (async D2H / H2D without implicit stream syncs)
+struct PinnedBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocDefault);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
 // All views of a problem live in ONE layered cudaArray (layer i = view i) behind
 // one texture object, so kernels sample any view through a warp-uniform handle.
 struct LayeredImages {
@@ -57,6 +79,7 @@ struct LayeredImages {
 struct acmmp_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    bool owns_stream = true;
     // event quads (start, after init, after sweeps, after tail) of every acmmp_run since the
     // last acmmp_timing_collect; the newest quad also serves acmmp_last_timing
     std::vector<cudaEvent_t> evpool;
@@ -70,12 +93,23 @@ struct acmmp_ctx {
     int W = 0, H = 0;
     std::vector<acmmp_camera> cams;
     LayeredImages views;
+    // resident path: all views of a scan live in one layered array owned by the scan;
+    // a problem then only names layers (no per-problem upload)
+    cudaTextureObject_t ext_tex = 0;
+    const float *ext_ref_image = nullptr;
+    std::vector<int> layers;   // layer of view i in the texture in use
     std::vector<DevBuf> depth_maps;   // per slot
     std::vector<int> depth_set;
     DevBuf ref_image, d_cams, d_depth_ptrs, d_rc, d_pairs, stage_in, stage_pad;
     DevBuf planes, costs, pre_costs, sel, rng, planes_snap, costs_snap;
     DevBuf seeded, prior_planes, plane_masks, scaled_planes, tmp_a, tmp_b, tmp_c, tri_buf;
-    std::vector<int32_t> h_cells, h_tris;
+    // planar-prior construction: pinned staging of the support cells / triangles, the
+    // event that marks the cells' arrival on the host, and the triangulation result
+    PinnedBuf h_cells, h_tris;
+    std::vector<int32_t> tri_scratch;
+    cudaEvent_t ev_cells = nullptr;
+    int prior_ns = 0, prior_nt = 0;
+    double prior_host_ms = 0.0;   // host time spent in compaction + Delaunay (sum)
     bool have_seeded = false, have_prior = false, have_scaled = false, have_warm = false;
     bool pairs_dirty = true;
     bool tail_done = false;
@@ -183,19 +217,54 @@ int refresh_pairs(acmmp_ctx *ctx) {
     std::vector<const float *> dptr(n, nullptr);
     for (int i = 0; i < n; ++i)
         if (i < (int)ctx->depth_maps.size() && ctx->depth_set[i]) dptr[i] = ctx->depth_maps[i].as<float>();
-    CU(ctx, ctx->d_cams.ensure(sizeof(acmmp_camera) * n));
-    CU(ctx, ctx->d_depth_ptrs.ensure(sizeof(float *) * n));
     CU(ctx, ctx->d_rc.ensure(ref_const_size()));
     CU(ctx, ctx->d_pairs.ensure(pair_const_size() * (n > 1 ? n - 1 : 1)));
-    // small synchronous copies from pageable host vectors: safe w.r.t. lifetime
-    CU(ctx, cudaMemcpyAsync(ctx->d_cams.p, ctx->cams.data(), sizeof(acmmp_camera) * n, cudaMemcpyHostToDevice, ctx->stream));
-    CU(ctx, cudaMemcpyAsync(ctx->d_depth_ptrs.p, dptr.data(), sizeof(float *) * n, cudaMemcpyHostToDevice, ctx->stream));
-    CU(ctx, cudaStreamSynchronize(ctx->stream));
-    CU(ctx, launch_setup_pairs(ctx->d_cams.as<acmmp_camera>(), n, ctx->d_depth_ptrs.as<const float *>(), ctx->params.depth_min, ctx->params.depth_max,
+    CU(ctx, launch_setup_pairs(ctx->cams.data(), n, dptr.data(), ctx->layers.data(), ctx->params.depth_min, ctx->params.depth_max,
                                ctx->d_rc.as<RefConst>(), ctx->d_pairs.as<PairConst>(), ctx->stream));
     ctx->launches++;
     ctx->pairs_dirty = false;
     return 0;
+}
+
+// per-problem state shared by the upload path (acmmp_set_problem) and the resident path
+int problem_common(acmmp_ctx *ctx, int n, const acmmp_camera *cams) {
+    ctx->W = cams[0].width;
+    ctx->H = cams[0].height;
+    const size_t P = (size_t)ctx->W * ctx->H;
+    CU(ctx, ctx->planes.ensure(P * sizeof(float4)));
+    CU(ctx, ctx->planes_snap.ensure(P * sizeof(float4)));
+    CU(ctx, ctx->costs.ensure(P * sizeof(float)));
+    CU(ctx, ctx->costs_snap.ensure(P * sizeof(float)));
+    CU(ctx, ctx->pre_costs.ensure(P * sizeof(float)));
+    CU(ctx, ctx->sel.ensure(P * sizeof(uint32_t)));
+    CU(ctx, ctx->rng.ensure(P * 6 * sizeof(uint32_t)));
+    // depth range widening + disparity range (ACMMP.cpp:600-606)
+    ctx->params.depth_min = cams[0].depth_min * 0.6f;
+    ctx->params.depth_max = cams[0].depth_max * 1.2f;
+    ctx->params.num_images = n;
+    ctx->params.disparity_min = cams[0].K[0] * ctx->params.baseline / ctx->params.depth_max;
+    ctx->params.disparity_max = cams[0].K[0] * ctx->params.baseline / ctx->params.depth_min;
+    ctx->depth_maps.resize(n);
+    ctx->depth_set.assign(n, 0);
+    ctx->have_seeded = ctx->have_prior = ctx->have_scaled = ctx->have_warm = false;
+    ctx->params.seeded = 0;
+    ctx->pairs_dirty = true;
+    ctx->tail_done = false;
+    return 0;
+}
+
+// resident path: the views already sit in layers of `tex` (owned by the caller);
+// ref_image = row-major reference image on the device (borrowed)
+int set_problem_resident(acmmp_ctx *ctx, int n, const acmmp_camera *cams, cudaTextureObject_t tex, const float *ref_image,
+                         const int *layers) {
+    if (n < 2 || n - 1 > ACMMP_MAX_SRC_VIEWS) return fail(ctx, ACMMP_ERR_INVALID, "need 1 reference + 1..%d source views, got n=%d", ACMMP_MAX_SRC_VIEWS, n);
+    if (bind_device(ctx)) return ACMMP_ERR_CUDA;
+    ctx->n = n;
+    ctx->cams.assign(cams, cams + n);
+    ctx->ext_tex = tex;
+    ctx->ext_ref_image = ref_image;
+    ctx->layers.assign(layers, layers + n);
+    return problem_common(ctx, n, cams);
 }
 
 }  // namespace
@@ -240,6 +309,27 @@ int acmmp_create(acmmp_ctx **out, int device) {
     return 0;
 }
 
+}  // extern "C"
+
+namespace {
+// a further context on the SAME stream as `first`: a second set of per-problem buffers so
+// that the host can prepare / finish one problem while the device works on another, with
+// all kernels still executing in issue order on one stream (no kernel concurrency, so
+// per-kernel event times stay meaningful)
+int create_sibling(acmmp_ctx **out, const acmmp_ctx *first) {
+    acmmp_ctx *ctx = new acmmp_ctx();
+    ctx->device = first->device;
+    ctx->stream = first->stream;
+    ctx->owns_stream = false;
+    acmmp_default_params(&ctx->params);
+    ctx->compat = first->compat;
+    *out = ctx;
+    return 0;
+}
+}  // namespace
+
+extern "C" {
+
 void acmmp_destroy(acmmp_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
@@ -253,7 +343,10 @@ void acmmp_destroy(acmmp_ctx *ctx) {
     for (auto *b : bufs) b->release();
     for (auto &ev : ctx->evpool)
         if (ev) cudaEventDestroy(ev);
-    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->ev_cells) cudaEventDestroy(ctx->ev_cells);
+    ctx->h_cells.release();
+    ctx->h_tris.release();
+    if (ctx->stream && ctx->owns_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
 
@@ -324,31 +417,20 @@ int acmmp_set_problem(acmmp_ctx *ctx, int n, const acmmp_camera *cams, const flo
         int rcode = upload_layer(ctx, i, images[i], cams[i].width, cams[i].height, images_on_device != 0);
         if (rcode) return rcode;
     }
-    ctx->W = cams[0].width;
-    ctx->H = cams[0].height;
-    const size_t P = (size_t)ctx->W * ctx->H;
-    CU(ctx, ctx->ref_image.ensure(P * sizeof(float)));
-    CU(ctx, cudaMemcpyAsync(ctx->ref_image.p, images[0], P * sizeof(float),
-                            images_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
-    CU(ctx, ctx->planes.ensure(P * sizeof(float4)));
-    CU(ctx, ctx->planes_snap.ensure(P * sizeof(float4)));
-    CU(ctx, ctx->costs.ensure(P * sizeof(float)));
-    CU(ctx, ctx->costs_snap.ensure(P * sizeof(float)));
-    CU(ctx, ctx->pre_costs.ensure(P * sizeof(float)));
-    CU(ctx, ctx->sel.ensure(P * sizeof(uint32_t)));
-    CU(ctx, ctx->rng.ensure(P * 6 * sizeof(uint32_t)));
-    // depth range widening + disparity range (ACMMP.cpp:600-606)
-    ctx->params.depth_min = cams[0].depth_min * 0.6f;
-    ctx->params.depth_max = cams[0].depth_max * 1.2f;
-    ctx->params.num_images = n;
-    ctx->params.disparity_min = cams[0].K[0] * ctx->params.baseline / ctx->params.depth_max;
-    ctx->params.disparity_max = cams[0].K[0] * ctx->params.baseline / ctx->params.depth_min;
-    ctx->depth_maps.resize(n);
-    ctx->depth_set.assign(n, 0);
-    ctx->have_seeded = ctx->have_prior = ctx->have_scaled = ctx->have_warm = false;
-    ctx->params.seeded = 0;
-    ctx->pairs_dirty = true;
-    ctx->tail_done = false;
+    ctx->ext_tex = 0;
+    ctx->ext_ref_image = nullptr;
+    ctx->layers.resize(n);
+    for (int i = 0; i < n; ++i) ctx->layers[i] = i;
+    {
+        const size_t P0 = (size_t)cams[0].width * cams[0].height;
+        CU(ctx, ctx->ref_image.ensure(P0 * sizeof(float)));
+        CU(ctx, cudaMemcpyAsync(ctx->ref_image.p, images[0], P0 * sizeof(float),
+                                images_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
+    }
+    {
+        int rcode = problem_common(ctx, n, cams);
+        if (rcode) return rcode;
+    }
     // host images may be freed by the caller right after this returns
     if (!images_on_device) CU(ctx, cudaStreamSynchronize(ctx->stream));
     return 0;

@@ -3,6 +3,8 @@
 // (-O3 --use_fast_math): see common.cuh for why.
 #include <curand_kernel.h>
 
+#include <cstring>
+
 #include "common.cuh"
 #include "geometry.cuh"
 #include "kernels.h"
@@ -26,9 +28,19 @@ ACMMP_DEV float dot3_ref_order(float a0, float b0, float a1, float b1, float a2,
     return ffma(a2, b2, ffma(a0, b0, fmul(a1, b1)));
 }
 
-__global__ void setup_pairs_kernel(const acmmp_camera *cams, int n, const float *const *depth_maps, float depth_min, float depth_max,
+// cameras and depth-map pointers travel as a kernel argument (<= 33 x 108 bytes):
+// no staging buffer, no host synchronisation per problem
+struct SetupArgs {
+    acmmp_camera cams[ACMMP_MAX_SRC_VIEWS + 1];
+    const float *depth[ACMMP_MAX_SRC_VIEWS + 1];
+    int layer[ACMMP_MAX_SRC_VIEWS + 1];   // layer of each view in the layered texture
+};
+
+__global__ void setup_pairs_kernel(const __grid_constant__ SetupArgs args, int n, int have_depth, float depth_min, float depth_max,
                                    RefConst *rc_out, PairConst *pairs_out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const acmmp_camera *cams = args.cams;
+    const float *const *depth_maps = have_depth ? args.depth : nullptr;
     const acmmp_camera &r = cams[0];
     if (i == 0) {
         RefConst rc;
@@ -64,7 +76,7 @@ __global__ void setup_pairs_kernel(const acmmp_camera *cams, int n, const float 
         pc.trel[a] = dot3_ref_order(s.R[3 * a + 0], c0, s.R[3 * a + 1], c1, s.R[3 * a + 2], c2);
     pc.K0s = s.K[0]; pc.K2s = s.K[2]; pc.K4s = s.K[4]; pc.K5s = s.K[5]; pc.K8s = s.K[8];
     pc.ws = (float)s.width; pc.hs = (float)s.height; pc.pad = 0.0f;
-    pc.layer = i + 1; pc.pad2 = 0;
+    pc.layer = args.layer[i + 1]; pc.pad2 = 0;
     for (int k = 0; k < 9; ++k) { pc.Rs[k] = s.R[k]; pc.Ks[k] = s.K[k]; }
     for (int k = 0; k < 3; ++k) pc.ts[k] = s.t[k];
     pc.Cs[0] = -nsc0; pc.Cs[1] = -nsc1; pc.Cs[2] = -nsc2;
@@ -291,9 +303,16 @@ __global__ void mufu_peak_kernel(float *out, int iters) {
 // ===========================================================================
 static inline dim3 grid2(int w, int h, int bx, int by) { return dim3((w + bx - 1) / bx, (h + by - 1) / by, 1); }
 
-cudaError_t launch_setup_pairs(const acmmp_camera *d_cams, int n, const float *const *d_depth_maps, float depth_min, float depth_max,
+cudaError_t launch_setup_pairs(const acmmp_camera *h_cams, int n, const float *const *h_depth_maps, const int *h_layers, float depth_min, float depth_max,
                                RefConst *d_rc, PairConst *d_pairs, cudaStream_t st) {
-    setup_pairs_kernel<<<1, 64, 0, st>>>(d_cams, n, d_depth_maps, depth_min, depth_max, d_rc, d_pairs);
+    SetupArgs args;
+    memset(&args, 0, sizeof args);
+    for (int i = 0; i < n; ++i) {
+        args.cams[i] = h_cams[i];
+        args.depth[i] = h_depth_maps ? h_depth_maps[i] : nullptr;
+        args.layer[i] = h_layers ? h_layers[i] : i;
+    }
+    setup_pairs_kernel<<<1, 64, 0, st>>>(args, n, h_depth_maps != nullptr, depth_min, depth_max, d_rc, d_pairs);
     return cudaGetLastError();
 }
 

@@ -47,7 +47,8 @@ struct SweepLaunch {
     int geom_consistency, planar_prior, hierarchy, compat;
 };
 
-cudaError_t launch_setup_pairs(const acmmp_camera *d_cams, int n, const float *const *d_depth_maps, float depth_min, float depth_max,
+// h_cams / h_depth_maps are HOST arrays (of device pointers for the depth maps): passed as a kernel argument
+cudaError_t launch_setup_pairs(const acmmp_camera *h_cams, int n, const float *const *h_depth_maps, const int *h_layers, float depth_min, float depth_max,
                                RefConst *d_rc, PairConst *d_pairs, cudaStream_t st);
 cudaError_t launch_rng_init(unsigned long long seed, int W, int H, uint32_t *d_rng6, cudaStream_t st);
 cudaError_t launch_init(const InitLaunch &L, cudaStream_t st);
@@ -65,7 +66,7 @@ cudaError_t launch_fp32_peak(float *scratch, int blocks, int threads, int iters,
 cudaError_t launch_mufu_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
 cudaError_t launch_support_cells(const float *costs, int W, int H, int2 *cells, cudaStream_t st);
 cudaError_t launch_tri_raster(const int *tris, int ntri, const float4 *planes, const RefConst *rc, int W,
-                              float4 *tri_planes, unsigned *labels, cudaStream_t st);
+                              float4 *tri_planes, unsigned *labels, int *big_list, cudaStream_t st);
 cudaError_t launch_prior_finalize(const unsigned *labels, const float4 *tri_planes, const RefConst *rc, int W, int H,
                                   float4 *prior_planes, unsigned *masks, cudaStream_t st);
 size_t pair_const_size();

@@ -339,6 +339,11 @@ class Scan:
     def sync(self):
         self._ck(self._lib.acmmp_scan_sync(self._s), "sync")
 
+    def host_stats(self):
+        a, b = C.c_double(), C.c_double()
+        self._ck(self._lib.acmmp_scan_host_stats(self._s, C.byref(a), C.byref(b)), "host_stats")
+        return {"prior_host_ms": a.value, "wait_ms": b.value}
+
     def reset(self):
         self._ck(self._lib.acmmp_scan_reset(self._s), "reset")
 

@@ -61,7 +61,7 @@ EXPORTS = [
     "acmmp_scan_create", "acmmp_scan_destroy", "acmmp_scan_last_error", "acmmp_scan_set_image",
     "acmmp_scan_set_shard", "acmmp_scan_set_sequential_geom", "acmmp_scan_num_levels", "acmmp_scan_begin_level",
     "acmmp_scan_run_stage", "acmmp_scan_exchange", "acmmp_scan_view_size", "acmmp_scan_get_view",
-    "acmmp_scan_timing", "acmmp_scan_sync", "acmmp_scan_reset", "acmmp_scan_mark", "acmmp_scan_elapsed",
+    "acmmp_scan_timing", "acmmp_scan_sync", "acmmp_scan_reset", "acmmp_scan_host_stats", "acmmp_scan_mark", "acmmp_scan_elapsed",
 ]
 
 _lib = None
@@ -140,6 +140,7 @@ def load():
     lib.acmmp_scan_timing.argtypes = [vp, C.POINTER(C.c_double * 4), C.POINTER(C.c_int), C.POINTER(C.c_uint64)]
     lib.acmmp_scan_sync.argtypes = [vp]
     lib.acmmp_scan_reset.argtypes = [vp]
+    lib.acmmp_scan_host_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.acmmp_scan_mark.argtypes = [vp, C.c_int]
     lib.acmmp_scan_elapsed.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float)]
     _lib = lib

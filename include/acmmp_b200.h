@@ -291,6 +291,10 @@ int acmmp_scan_get_view(acmmp_scan *s, int view, float *depth, float *normal3, f
  * *launches = kernel launches so far. */
 int acmmp_scan_timing(acmmp_scan *s, double out_ms[4], int *runs, uint64_t *launches);
 int acmmp_scan_sync(acmmp_scan *s);
+/* host-side cost of the planar-prior triangulation since the last call: total host
+ * ms spent in compaction + Delaunay (worker threads) and ms the issuing thread was
+ * blocked waiting for one (0 = fully hidden behind device work). */
+int acmmp_scan_host_stats(acmmp_scan *s, double *prior_host_ms, double *wait_ms);
 /* start the schedule over (level 0 next) keeping images and buffers */
 int acmmp_scan_reset(acmmp_scan *s);
 /* CUDA events on the scan's stream: record mark i (0..7); elapsed ms between

@@ -21,6 +21,7 @@ ap.add_argument("--height", type=int, default=960)
 ap.add_argument("--nsrc", type=int, default=4)
 ap.add_argument("--device", default="cuda")
 ap.add_argument("--sequential", action="store_true")
+ap.add_argument("--passes", type=int, default=1)
 args = ap.parse_args()
 
 t0 = time.time()
@@ -33,15 +34,25 @@ for v, im in enumerate(sc["images"]):
 nl = scan.num_levels()
 print("levels", nl)
 names = ["photo+prior", "geom0", "geom1"]
+for p_ in range(args.passes - 1):       # warm-up passes (allocations, thread pools)
+    scan.reset()
+    scan.run_all(1234)
+    scan.sync()
+    scan.timing(); scan.host_stats()
+scan.reset()
 t_all = time.time()
 for level in range(nl):
+    t = time.time()
     scan.begin_level(level)
+    scan.sync()
+    print(json.dumps({"level": level, "begin_level_wall_s": round(time.time() - t, 3)}), flush=True)
     for st in range(3):
         t = time.time()
         scan.run_stage(st, 1234)
         scan.sync()
         wall = time.time() - t
         tm = scan.timing()
+        hs = scan.host_stats()
         acc = []
         for v in (0, args.views // 2):
             d, n, c = scan.get_view(v)
@@ -53,5 +64,5 @@ for level in range(nl):
             err = np.abs(d - gt) / gt
             acc.append(round(float((err[8:-8, 8:-8] < 0.01).mean()), 4))
         print(json.dumps({"level": level, "stage": names[st], "wall_s": round(wall, 3), "kernel_ms": round(tm["total_ms"], 1),
-                          "sweeps_ms": round(tm["sweeps_ms"], 1), "runs": tm["runs"], "acc<1%": acc, "size": list(d.shape)}), flush=True)
+                          "sweeps_ms": round(tm["sweeps_ms"], 1), "runs": tm["runs"], "prior_host_ms": round(hs["prior_host_ms"], 1), "wait_ms": round(hs["wait_ms"], 1), "acc<1%": acc, "size": list(d.shape)}), flush=True)
 print("total wall s", round(time.time() - t_all, 2), "views/s", round(args.views / (time.time() - t_all), 3))
