@@ -329,7 +329,7 @@ size_t init_smem_bytes(int nsrc) {
     per_group = (per_group + 15) & ~(size_t)15;
     size_t pairs = ((size_t)nsrc * sizeof(PairConst) + 15) & ~(size_t)15;
     size_t rc = (sizeof(RefConst) + 15) & ~(size_t)15;
-    return pairs + rc + per_group * kGroupsPerCta;
+    return pairs + rc + per_group * kInitGroups;
 }
 
 cudaError_t launch_init(const InitLaunch &L, cudaStream_t st) {
@@ -348,7 +348,7 @@ cudaError_t launch_init(const InitLaunch &L, cudaStream_t st) {
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    init_kernel<<<grid2(L.W, L.H, 8, 4), kSweepThreads, smem, st>>>(a);
+    init_kernel<<<grid2(L.W, L.H, 8, 4), kInitThreads, smem, st>>>(a);
     return cudaGetLastError();
 }
 

@@ -34,9 +34,14 @@
 namespace acmmp {
 
 constexpr int kGroup = 8;                 // lanes per pixel
-constexpr int kGroupsPerCta = 32;         // pixels per CTA
+#ifndef ACMMP_SWEEP_GROUPS
+#define ACMMP_SWEEP_GROUPS 32
+#endif
+constexpr int kGroupsPerCta = ACMMP_SWEEP_GROUPS;   // pixels per CTA (multiple of 8)
 constexpr int kSweepThreads = kGroup * kGroupsPerCta;
-constexpr int kTileW = 16, kTileH = 4;    // 64 pixels, 32 of each colour
+constexpr int kTileW = 16, kTileH = kGroupsPerCta / 8;   // 16 x kTileH pixels, half of each colour
+constexpr int kInitGroups = 32;           // init_kernel: 8 x 4 pixel tile
+constexpr int kInitThreads = kGroup * kInitGroups;
 
 struct SweepArgs {
     // snapshot (read) and live (write) state

@@ -5,7 +5,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libacmmp_b200.so")
+LIB_PATH = os.environ.get("ACMMP_B200_LIB") or os.path.join(_HERE, "libacmmp_b200.so")   # override: kernel-variant experiments
 
 MAX_SRC_VIEWS = 32
 COMPAT_REF_SM100 = 0

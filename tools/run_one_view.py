@@ -25,5 +25,9 @@ m = host.ACMMP(0)
 m.InputInitialization([sc["images"][i] for i in ids], [sc["cams"][i] for i in ids])
 for r in range(args.runs):
     m.RunPatchMatch(1234)
-    print(json.dumps(m.last_timing()))
+    t = m.last_timing()
+    planes, cost = m.GetPlaneHypotheses(), m.GetCosts()
+    import zlib
+    t["crc"] = zlib.crc32(planes.tobytes()) ^ zlib.crc32(cost.tobytes())
+    print(json.dumps(t))
 print("launches", m.launch_count())
