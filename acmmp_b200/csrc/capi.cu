@@ -114,6 +114,9 @@ struct acmmp_ctx {
     bool pairs_dirty = true;
     bool tail_done = false;
     uint64_t launches = 0;
+    uint64_t init_ncc = 0;       // NCC evaluations issued by init_kernel since the last acmmp_ncc_count
+    int count_ncc = 0;           // sweep_kernel instrumentation on / off
+    DevBuf ncc_counter;
     float timing[4] = {0, 0, 0, 0};
 };
 
@@ -339,7 +342,7 @@ void acmmp_destroy(acmmp_ctx *ctx) {
     DevBuf *bufs[] = {&ctx->ref_image, &ctx->d_cams, &ctx->stage_in, &ctx->stage_pad, &ctx->d_depth_ptrs, &ctx->d_rc, &ctx->d_pairs,
                       &ctx->planes, &ctx->costs, &ctx->pre_costs, &ctx->sel, &ctx->rng, &ctx->planes_snap,
                       &ctx->costs_snap, &ctx->seeded, &ctx->prior_planes, &ctx->plane_masks, &ctx->scaled_planes,
-                      &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c, &ctx->tri_buf};
+                      &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c, &ctx->tri_buf, &ctx->ncc_counter};
     for (auto *b : bufs) b->release();
     for (auto &ev : ctx->evpool)
         if (ev) cudaEventDestroy(ev);

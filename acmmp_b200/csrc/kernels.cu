@@ -362,6 +362,7 @@ cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st) {
     a.sigma_spatial = L.sigma_spatial; a.sigma_color = L.sigma_color;
     a.geom_consistency = L.geom_consistency; a.planar_prior = L.planar_prior; a.hierarchy = L.hierarchy;
     a.compat = L.compat;
+    a.ncc_counter = L.ncc_counter;
     const size_t smem = sweep_smem_bytes(L.nsrc);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
@@ -407,6 +408,35 @@ cudaError_t launch_resize_linear(const float *src, int sw, int sh, float *dst, i
 
 cudaError_t launch_pad_replicate(const float *src, int w, int h, float *dst, int W, int H, cudaStream_t st) {
     pad_replicate_kernel<<<grid2(W, H, 32, 8), dim3(32, 8), 0, st>>>(src, w, h, dst, W, H);
+    return cudaGetLastError();
+}
+
+// bilinear fetch rate of a layered R32F texture.  mode 0: a warp reads 32 horizontally
+// adjacent pixels (best case); mode 1: the sweep kernel's shape - 8 lanes around each of
+// 4 pixels, a few pixels apart, taps advancing by 2 pixels.
+__global__ void tex_peak_kernel(cudaTextureObject_t tex, int w, int h, int layers, int iters, int mode, float *out) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = tid >> 5;
+    float bx, by;
+    if (mode == 0) {
+        bx = (float)((warp * 32) % w + lane) + 0.37f;
+        by = (float)((warp * 7) % h) + 0.61f;
+    } else {
+        bx = (float)((warp * 8) % w + 2 * (lane >> 3)) + 1.7f * (float)(lane & 7) + 0.37f;
+        by = (float)((warp * 5) % h) + 0.9f * (float)(lane & 7) + 0.61f;
+    }
+    const int layer = warp % layers;
+    float acc = 0.0f;
+    for (int i = 0; i < iters; ++i) {
+        const float x = bx + (float)(2 * (i % 6));
+        const float y = by + (float)(2 * ((i / 6) % 6)) + (float)(i / 36);
+        acc += tex2DLayered<float>(tex, x, y, layer);
+    }
+    if (acc == 123.456f) out[tid] = acc;   // keeps the loop alive
+}
+cudaError_t launch_tex_peak(cudaTextureObject_t tex, int w, int h, int layers, int blocks, int threads, int iters, int mode,
+                            float *scratch, cudaStream_t st) {
+    tex_peak_kernel<<<blocks, threads, 0, st>>>(tex, w, h, layers, iters, mode, scratch);
     return cudaGetLastError();
 }
 

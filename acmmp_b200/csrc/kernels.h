@@ -45,6 +45,7 @@ struct SweepLaunch {
     int W, H, nsrc, iter, color;
     float sigma_spatial, sigma_color;
     int geom_consistency, planar_prior, hierarchy, compat;
+    unsigned long long *ncc_counter;   // nullable; 4096 slots
 };
 
 // h_cams / h_depth_maps are HOST arrays (of device pointers for the depth maps): passed as a kernel argument
@@ -63,6 +64,8 @@ cudaError_t launch_jbu_depth(const float *image, int w, int h, const float *sdep
 cudaError_t launch_resize_linear(const float *src, int sw, int sh, float *dst, int dw, int dh, cudaStream_t st);
 cudaError_t launch_pad_replicate(const float *src, int w, int h, float *dst, int W, int H, cudaStream_t st);
 cudaError_t launch_fp32_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
+cudaError_t launch_tex_peak(cudaTextureObject_t tex, int w, int h, int layers, int blocks, int threads, int iters, int mode,
+                            float *scratch, cudaStream_t st);
 cudaError_t launch_mufu_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
 cudaError_t launch_support_cells(const float *costs, int W, int H, int2 *cells, cudaStream_t st);
 cudaError_t launch_tri_raster(const int *tris, int ntri, const float4 *planes, const RefConst *rc, int W,

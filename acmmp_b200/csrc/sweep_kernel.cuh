@@ -64,7 +64,9 @@ struct SweepArgs {
     float sigma_spatial, sigma_color;
     int geom_consistency, planar_prior, hierarchy;
     int compat;               // acmmp_compat_mode
+    unsigned long long *ncc_counter;   // optional instrumentation: kNccCounterSlots slots, NCC evaluations issued
 };
+constexpr int kNccCounterSlots = 4096;
 
 // Per-pixel shared-memory block.  nsrc-sized arrays follow the fixed part.
 struct GroupSmemFixed {

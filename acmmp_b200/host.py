@@ -245,6 +245,14 @@ def measure_fp32_peak(device=0):
     return a.value, b.value
 
 
+def measure_tex_peak(device=0):
+    """(coherent, grouped) bilinear fetch rate in G fetches/s: the propagation kernel's roofline."""
+    lib = L.load()
+    a, b = C.c_double(), C.c_double()
+    _check(None, lib.acmmp_measure_tex_peak(device, C.byref(a), C.byref(b)), "measure_tex_peak")
+    return a.value, b.value
+
+
 STAGE_PHOTO, STAGE_GEOM0, STAGE_GEOM1 = 0, 1, 2
 
 
@@ -343,6 +351,15 @@ class Scan:
         a, b = C.c_double(), C.c_double()
         self._ck(self._lib.acmmp_scan_host_stats(self._s, C.byref(a), C.byref(b)), "host_stats")
         return {"prior_host_ms": a.value, "wait_ms": b.value}
+
+    def count_ncc(self, enable=True):
+        """switch the device-side count of NCC evaluations on / off (instrumentation)"""
+        self._ck(self._lib.acmmp_scan_count_ncc(self._s, int(bool(enable))), "count_ncc")
+
+    def ncc_count(self):
+        a, b = C.c_uint64(), C.c_uint64()
+        self._ck(self._lib.acmmp_scan_ncc_count(self._s, C.byref(a), C.byref(b)), "ncc_count")
+        return {"init": a.value, "sweeps": b.value}
 
     def reset(self):
         self._ck(self._lib.acmmp_scan_reset(self._s), "reset")

@@ -57,7 +57,8 @@ EXPORTS = [
     "acmmp_run_sweep", "acmmp_run_tail", "acmmp_get_result", "acmmp_get_maps",
     "acmmp_get_depth_device", "acmmp_get_state", "acmmp_set_state", "acmmp_width", "acmmp_height",
     "acmmp_sync", "acmmp_launch_count", "acmmp_last_timing", "acmmp_jbu_depth", "acmmp_resize_linear",
-    "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_get_planar_prior", "acmmp_delaunay", "acmmp_timing_collect",
+    "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_measure_tex_peak", "acmmp_get_planar_prior", "acmmp_delaunay", "acmmp_timing_collect",
+    "acmmp_count_ncc", "acmmp_ncc_count", "acmmp_scan_count_ncc", "acmmp_scan_ncc_count",
     "acmmp_scan_create", "acmmp_scan_destroy", "acmmp_scan_last_error", "acmmp_scan_set_image",
     "acmmp_scan_set_shard", "acmmp_scan_set_sequential_geom", "acmmp_scan_num_levels", "acmmp_scan_begin_level",
     "acmmp_scan_run_stage", "acmmp_scan_exchange", "acmmp_scan_view_size", "acmmp_scan_get_view",
@@ -122,6 +123,7 @@ def load():
     lib.acmmp_resize_linear.argtypes = [C.c_int, fp, C.c_int, C.c_int, fp, C.c_int, C.c_int]
     lib.acmmp_rng_init_states.argtypes = [C.c_int, C.c_uint64, C.c_int, C.c_int, up]
     lib.acmmp_measure_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.acmmp_measure_tex_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     i32p = C.POINTER(C.c_int32)
     lib.acmmp_scan_create.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.POINTER(Camera), i32p, i32p]
     lib.acmmp_scan_destroy.argtypes = [vp]
@@ -141,6 +143,10 @@ def load():
     lib.acmmp_scan_sync.argtypes = [vp]
     lib.acmmp_scan_reset.argtypes = [vp]
     lib.acmmp_scan_host_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.acmmp_scan_count_ncc.argtypes = [vp, C.c_int]
+    lib.acmmp_scan_ncc_count.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    lib.acmmp_count_ncc.argtypes = [vp, C.c_int]
+    lib.acmmp_ncc_count.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.acmmp_scan_mark.argtypes = [vp, C.c_int]
     lib.acmmp_scan_elapsed.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float)]
     _lib = lib

@@ -24,6 +24,9 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 FLOP_PER_NCC = 1538.0          # 36 x 38 + 170
+# dram__bytes_read.sum + dram__bytes_write.sum of one sweep_kernel launch at 1600x1200, 10 sources
+# (ncu --set full, profiles/r1e_sweep_full_summary.txt); ~0.7 % of what HBM could move in that time
+SWEEP_DRAM_BYTES_PER_LAUNCH = 325.3e6
 HYP_PER_RUN = 29               # 1 (init) + 2 x 14; 30 for the hierarchy (upsample-init) run
 
 
@@ -198,14 +201,30 @@ def run_ours(args):
         scan.begin_level(lvl)
         sizes.append(scan.view_size(0))
     scan.sync()
+    # executed work: one extra, untimed step with the device-side NCC counter switched on
+    scan.count_ncc(True)
+    scan.ncc_count()
+    ex0 = n_exchanges[0]
+    step(False)
+    scan.sync()
+    exchanges_per_step = n_exchanges[0] - ex0
+    ncc = scan.ncc_count()
+    scan.count_ncc(False)
     fp32_tflops, mufu_gops = host.measure_fp32_peak(local)
+    tex_coherent, tex_grouped = host.measure_tex_peak(local)
     hpv = hyp_evals_per_view(sizes)
     views_per_s = n * args.steps / (ms_dev * 1e-3)
     e2e_views_per_s = n * args.steps / (ms_e2e * 1e-3)
-    # dominant kernel: sweep_kernel.  algorithmic NCC evaluations of rank 0's runs in the
-    # timed region: per run P * 28 hypotheses * nsrc views
+    # dominant kernel: sweep_kernel (rank 0's launches in the timed region).
+    #  reference formulation: per run P * 28 hypotheses * nsrc views, 1538 flop each
+    #  executed: counted NCC evaluations x 36 bilinear fetches (the kernel scores the current plane and
+    #  the 5 refinement candidates against the sampled views only)
     ncc_sweeps = sum(4 * w * h * 28 * args.nsrc for (w, h) in sizes) * len(owned) * args.steps
-    achieved = ncc_sweeps * FLOP_PER_NCC / (tm["sweeps_ms"] * 1e-3) / 1e12
+    sweep_s = tm["sweeps_ms"] * 1e-3
+    fp32_achieved = ncc_sweeps * FLOP_PER_NCC / sweep_s / 1e12
+    fetches = ncc["sweeps"] * 36 * args.steps
+    tex_achieved = fetches / sweep_s / 1e9
+    n_sweep_launches = 4 * 4 * len(owned) * len(sizes) * args.steps   # 4 runs x 4 half-sweeps per view per level
     h2d = sum(int(np.prod(im.shape)) * 4 for im in imgs_np)
     d2h = len(owned) * H * W * 5 * 4
     line = {
@@ -223,13 +242,21 @@ def run_ours(args):
                 "ms_per_step": ms_e2e / args.steps, "mpix_hyp_per_s": e2e_views_per_s * hpv / 1e6},
         "gpu_launches": int(launches),
         "kernel_ms_per_step": {k: tm[k] / args.steps for k in ("init_ms", "sweeps_ms", "tail_ms", "total_ms")},
-        "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_tflops, "unit": "TFLOP/s", "frac": achieved / fp32_tflops,
-                     "traffic": None, "kernel": "sweep_kernel",
-                     "note": "FP32/texture-bound path (no HBM or tensor bound applies): achieved = algorithmic NCC evaluations x 1538 flop / "
-                             "sweep_kernel time (CUDA events on the launching stream); peak = FP32 FMA rate measured live by fp32_peak_kernel "
-                             "(MEASURED_PEAKS.json has no FP32 figure)", "mufu_gops_measured": mufu_gops},
+        "roofline": {"bound": "tex", "kernel": "sweep_kernel", "achieved": tex_achieved, "peak": tex_coherent, "unit": "Gfetch/s",
+                     "frac": tex_achieved / tex_coherent, "traffic": SWEEP_DRAM_BYTES_PER_LAUNCH,
+                     "launches": n_sweep_launches, "avg_launch_ms": tm["sweeps_ms"] / n_sweep_launches,
+                     "fetches_per_launch": fetches / n_sweep_launches, "peak_grouped_access": tex_grouped,
+                     "fp32": {"achieved": fp32_achieved, "peak": fp32_tflops, "unit": "TFLOP/s", "frac": fp32_achieved / fp32_tflops,
+                              "mufu_gops_measured": mufu_gops},
+                     "ncc_evals_per_step": {"init": ncc["init"], "sweeps": ncc["sweeps"], "reference_formulation": ncc_sweeps // args.steps},
+                     "note": "texture-pipe bound (ncu: l1tex data-stage is the top unit; HBM traffic is ~0.7 % of peak, no tensor-shaped work): "
+                             "achieved = bilinear fetches issued by sweep_kernel (device-counted NCC evaluations x 36) / its time from CUDA events "
+                             "on the launching stream; peak = fetch rate of tex_peak_kernel measured live on this GPU with warp-coherent "
+                             "coordinates (peak_grouped_access: same with the kernel's 8-hypotheses-per-pixel shape). fp32: SURVEY.md 8(d)'s "
+                             "reference-formulation flop (NCC x 1538) against the live FP32 FMA peak. traffic = dram bytes per launch from the "
+                             "ncu --set full capture in profiles/ (1600x1200 level)"},
         "clocks": clocks.summary(),
-        "exchanges_per_step": n_exchanges[0] // max(1, (args.warmup + 2 * args.steps + 1)),
+        "exchanges_per_step": exchanges_per_step,
     }
     if rank == 0 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args, sc, hpv)

@@ -229,9 +229,21 @@ int acmmp_resize_linear(int device, const float *src, int sw, int sh,
 int acmmp_rng_init_states(int device, uint64_t seed, int w, int h,
                           uint32_t *rng6);
 
+/* ---- instrumentation ------------------------------------------------------------
+ * NCC evaluations (one pixel x hypothesis x source view = 36 bilinear fetches)
+ * issued since the last call: by the initial-cost kernel (exact, from the problem
+ * size) and by the propagation kernel (counted on the device when enabled with
+ * acmmp_count_ncc; off by default).  Used for the executed-work side of the roofline. */
+int acmmp_count_ncc(acmmp_ctx *ctx, int enable);
+int acmmp_ncc_count(acmmp_ctx *ctx, uint64_t *init_ncc, uint64_t *sweep_ncc);
+
 /* ---- micro-benchmarks used by bench.py for the roofline denominators --------
  * measured FP32 FMA throughput (TFLOP/s), MUFU rate (Gop/s). */
 int acmmp_measure_fp32_peak(int device, double *tflops, double *mufu_gops);
+/* measured bilinear fetch rate (G fetches/s) of a layered R32F texture of one
+ * DTU-shape problem: warp-coherent coordinates, and the propagation kernel's
+ * access shape (8 hypotheses around each of 4 pixels per warp). */
+int acmmp_measure_tex_peak(int device, double *coherent_gfetch, double *grouped_gfetch);
 
 /* ==== whole-scan schedule ======================================================
  * The stage graph of main() (/root/reference/src/main_ACMMP.cpp:89-176) over a
@@ -295,6 +307,9 @@ int acmmp_scan_sync(acmmp_scan *s);
  * ms spent in compaction + Delaunay (worker threads) and ms the issuing thread was
  * blocked waiting for one (0 = fully hidden behind device work). */
 int acmmp_scan_host_stats(acmmp_scan *s, double *prior_host_ms, double *wait_ms);
+/* acmmp_count_ncc / acmmp_ncc_count over every buffer set of the scan */
+int acmmp_scan_count_ncc(acmmp_scan *s, int enable);
+int acmmp_scan_ncc_count(acmmp_scan *s, uint64_t *init_ncc, uint64_t *sweep_ncc);
 /* start the schedule over (level 0 next) keeping images and buffers */
 int acmmp_scan_reset(acmmp_scan *s);
 /* CUDA events on the scan's stream: record mark i (0..7); elapsed ms between
