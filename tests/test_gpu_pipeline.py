@@ -134,6 +134,43 @@ def test_half_sweeps_step_exact_vs_live_reference_kernels():
     ref.close()
 
 
+@needs_ref
+def test_hierarchy_upsample_init_bit_exact_vs_live_reference_kernels():
+    """RandomInitialization in hierarchy + upsample mode (ACMMP.cu:663-689): joint-bilateral
+    upsampling of the coarse normals, cost of the uploaded JBU-depth plane (pre_costs) and of
+    the upsampled plane, view masks."""
+    sc = make_scene(5, 320, 240, 4, seed=3)
+    images, cams, ids = problem(sc, 0)
+    h, w, ch, cw = 240, 320, 120, 160
+    rng = np.random.default_rng(5)
+    cn = rng.normal(size=(ch, cw, 3)).astype(np.float32) * np.float32(0.2) + np.array([0, 0, -1], np.float32)
+    cn /= np.linalg.norm(cn, axis=-1, keepdims=True)
+    cn = np.ascontiguousarray(cn, np.float32)
+    cc = rng.uniform(0.0, 0.6, size=(ch, cw)).astype(np.float32)
+    fd = np.ascontiguousarray(sc["depths"][0] * (1.0 + 0.01 * rng.standard_normal((h, w))), np.float32)
+    ref = refbind.RefACMMP(0)
+    ref.set_problem(images, cams)
+    ref.set_flags(hierarchy=1, upsample=1, scaled_cols=float(cw), scaled_rows=float(ch))
+    ref.set_planes(3, np.concatenate([cn, cc[..., None]], -1))
+    fp = np.zeros((h, w, 4), np.float32)
+    fp[..., 3] = fd
+    ref.set_planes(0, fp)
+    ref.run_init(321)
+    rp, rc_, rs, rr, rpre = ref.get_state()
+    m = host.ACMMP(0)
+    m.SetHierarchyParams()
+    m.InputInitialization(images, cams)
+    m.CudaSpaceInitialization(hierarchy=(cn, cc, fd))
+    m.run_init(321)
+    mp, mc, ms, mr = m.get_state()
+    same_p = (gu.bits(mp) == gu.bits(rp)).all(-1)
+    same_c = gu.bits(mc) == gu.bits(rc_)
+    assert same_p.mean() == 1.0 and same_c.mean() == 1.0 and (ms == rs).all() and (mr == rr).all(), \
+        (same_p.mean(), same_c.mean(), (ms == rs).mean(), (mr == rr).mean())
+    m.close()
+    ref.close()
+
+
 def run_scan(sc, world=1, seed=77, sequential=False):
     """full schedule; world > 1 = logical shards executed one after the other on this
     GPU, exchanging their depth-map segments like the NCCL all-gather would."""
