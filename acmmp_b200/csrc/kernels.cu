@@ -325,7 +325,7 @@ cudaError_t launch_rng_init(unsigned long long seed, int W, int H, uint32_t *d_r
 }
 
 size_t init_smem_bytes(int nsrc) {
-    size_t per_group = sizeof(GroupSmemFixed) + (size_t)nsrc * sizeof(float);
+    size_t per_group = sizeof(GroupSmemFixed) + (size_t)2 * nsrc * sizeof(float);
     per_group = (per_group + 15) & ~(size_t)15;
     size_t pairs = ((size_t)nsrc * sizeof(PairConst) + 15) & ~(size_t)15;
     size_t rc = (sizeof(RefConst) + 15) & ~(size_t)15;
@@ -348,7 +348,7 @@ cudaError_t launch_init(const InitLaunch &L, cudaStream_t st) {
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    init_kernel<<<grid2(L.W, L.H, 8, 4), kInitThreads, smem, st>>>(a);
+    init_kernel<<<grid2(L.W, L.H, kInitTileW, kInitTileH), kInitThreads, smem, st>>>(a);
     return cudaGetLastError();
 }
 

@@ -40,8 +40,10 @@ constexpr int kGroup = 8;                 // lanes per pixel
 constexpr int kGroupsPerCta = ACMMP_SWEEP_GROUPS;   // pixels per CTA (multiple of 8)
 constexpr int kSweepThreads = kGroup * kGroupsPerCta;
 constexpr int kTileW = 16, kTileH = kGroupsPerCta / 8;   // 16 x kTileH pixels, half of each colour
-constexpr int kInitGroups = 32;           // init_kernel: 8 x 4 pixel tile
-constexpr int kInitThreads = kGroup * kInitGroups;
+constexpr int kInitGroup = 4;             // init_kernel: lanes per pixel
+constexpr int kInitTileW = 16, kInitTileH = 4;
+constexpr int kInitGroups = kInitTileW * kInitTileH;   // pixels per CTA
+constexpr int kInitThreads = kInitGroup * kInitGroups;
 
 struct SweepArgs {
     // snapshot (read) and live (write) state
