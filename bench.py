@@ -25,8 +25,9 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 FLOP_PER_NCC = 1538.0          # 36 x 38 + 170
 # dram__bytes_read.sum + dram__bytes_write.sum of one sweep_kernel launch at 1600x1200, 10 sources
-# (ncu --set full, profiles/r1e_sweep_full_summary.txt); ~0.7 % of what HBM could move in that time
-SWEEP_DRAM_BYTES_PER_LAUNCH = 325.3e6
+# (ncu --set full, profiles/r1g_sweep_init_full_summary.txt: 311 MB read + 121 MB written, average of 8
+# launches); ~1 % of what HBM could move in that time
+SWEEP_DRAM_BYTES_PER_LAUNCH = 432e6
 HYP_PER_RUN = 29               # 1 (init) + 2 x 14; 30 for the hierarchy (upsample-init) run
 
 
