@@ -13,8 +13,15 @@ REF       := /root/reference/src
 
 all: $(LIB) oracle
 
-$(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp -lcudart
+# fusion.cu restates host code of the reference (IEEE float / double): no fast math, no contraction
+FUSIONFLAGS := -O3 -std=c++17 $(ARCH) -lineinfo -fmad=false -Xcompiler -fPIC
+
+build/fusion.o: $(CSRC)/fusion.cu include/acmmp_b200.h
+	@mkdir -p build
+	$(NVCC) $(FUSIONFLAGS) -c -o $@ $(CSRC)/fusion.cu
+
+$(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp build/fusion.o $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp build/fusion.o -lcudart
 
 oracle: oracle/liboracle.so
 

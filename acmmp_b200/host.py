@@ -338,6 +338,12 @@ class Scan:
         self._ck(self._lib.acmmp_scan_get_view(self._s, view, L.fptr(d), L.fptr(n), L.fptr(c)), "get_view")
         return d, n, c
 
+    def view_device(self, view):
+        """(depth, normal3, cost) device pointers of an owned view (ints)"""
+        d, n, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self._ck(self._lib.acmmp_scan_view_device(self._s, view, C.byref(d), C.byref(n), C.byref(c)), "view_device")
+        return d.value, n.value, c.value
+
     def timing(self):
         out, runs, launches = (C.c_double * 4)(), C.c_int(), C.c_uint64()
         self._ck(self._lib.acmmp_scan_timing(self._s, C.byref(out), C.byref(runs), C.byref(launches)), "timing")
@@ -382,3 +388,86 @@ class Scan:
                 self.run_stage(st, seed)
                 if exchange is not None:
                     exchange(*self.exchange_info())
+
+
+class Fusion:
+    """RunFusion (acmmp_definitions.cpp:828-1043) on the device, without the file I/O:
+    `cams` are the cameras rescaled to the depth maps, `pairs[v]` the source-view indices."""
+
+    def __init__(self, cams, pairs, device=0):
+        self._lib = L.load()
+        self._f = C.c_void_p()
+        n = len(cams)
+        cam_arr = (L.Camera * n)(*[c.copy() for c in cams])
+        offs = np.zeros(n + 1, np.int32)
+        for i, p in enumerate(pairs):
+            offs[i + 1] = offs[i] + len(p)
+        ids = np.ascontiguousarray([j for p in pairs for j in p], np.int32)
+        i32 = C.POINTER(C.c_int32)
+        rc = self._lib.acmmp_fusion_create(C.byref(self._f), device, n, cam_arr, offs.ctypes.data_as(i32), ids.ctypes.data_as(i32))
+        if rc != 0:
+            raise L.AcmmpError(f"acmmp_fusion_create failed ({rc}): {self._lib.acmmp_fusion_last_error(None).decode()}")
+        self.n = n
+        self.sizes = [(c.height, c.width) for c in cams]
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise L.AcmmpError(f"{what} failed ({rc}): {self._lib.acmmp_fusion_last_error(self._f).decode()}")
+
+    def close(self):
+        if self._f:
+            self._lib.acmmp_fusion_destroy(self._f)
+            self._f = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_view(self, view, depth, normal, color=None, mask=None, on_device=False):
+        """numpy arrays, or raw device pointers (ints) with on_device=True"""
+        if on_device:
+            ptrs = [C.c_void_p(int(p)) if p else None for p in (depth, normal, color, mask)]
+        else:
+            keep = [L.f32(depth), L.f32(normal),
+                    None if color is None else np.ascontiguousarray(color, np.uint8),
+                    None if mask is None else np.ascontiguousarray(mask, np.uint8)]
+            ptrs = [None if a is None else C.c_void_p(a.ctypes.data) for a in keep]
+        self._ck(self._lib.acmmp_fusion_set_view(self._f, view, ptrs[0], ptrs[1], ptrs[2], ptrs[3], int(on_device)), "fusion_set_view")
+
+    def run(self, consistency_scalar=0.3, con_num_thresh=1):
+        n = C.c_int64()
+        self._ck(self._lib.acmmp_fusion_run(self._f, float(consistency_scalar), int(con_num_thresh), C.byref(n)), "fusion_run")
+        self.num_points = n.value
+        return n.value
+
+    def points(self):
+        pts = np.empty((self.num_points, 9), np.float32)
+        per = (C.c_int64 * self.n)()
+        self._ck(self._lib.acmmp_fusion_get_points(self._f, C.c_void_p(pts.ctypes.data), self.num_points, per), "fusion_get_points")
+        return pts, list(per)
+
+    def mask(self, view):
+        h, w = self.sizes[view]
+        out = np.empty((h, w), np.uint8)
+        self._ck(self._lib.acmmp_fusion_get_mask(self._f, view, C.c_void_p(out.ctypes.data)), "fusion_get_mask")
+        return out
+
+    def stats(self):
+        ms = (C.c_double * 3)()
+        rounds = (C.c_int32 * self.n)()
+        self._ck(self._lib.acmmp_fusion_stats(self._f, ms, rounds), "fusion_stats")
+        return {"score_ms": ms[0], "greedy_ms": ms[1], "emit_ms": ms[2], "rounds": list(rounds)}
+
+
+def RunFusion(cams, pairs, depths, normals, colors=None, masks=None, consistency_scalar=0.3, con_num_thresh=1, device=0):
+    """RunFusion with in-memory maps: returns (points[N, 9], per-view accepted counts)."""
+    f = Fusion(cams, pairs, device)
+    try:
+        for v in range(len(cams)):
+            f.set_view(v, depths[v], normals[v], None if colors is None else colors[v], None if masks is None else masks[v])
+        f.run(consistency_scalar, con_num_thresh)
+        return f.points()
+    finally:
+        f.close()

@@ -59,9 +59,11 @@ EXPORTS = [
     "acmmp_sync", "acmmp_launch_count", "acmmp_last_timing", "acmmp_jbu_depth", "acmmp_resize_linear",
     "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_measure_tex_peak", "acmmp_get_planar_prior", "acmmp_delaunay", "acmmp_timing_collect",
     "acmmp_count_ncc", "acmmp_ncc_count", "acmmp_scan_count_ncc", "acmmp_scan_ncc_count",
+    "acmmp_fusion_create", "acmmp_fusion_destroy", "acmmp_fusion_last_error", "acmmp_fusion_set_view", "acmmp_fusion_run",
+    "acmmp_fusion_get_points", "acmmp_fusion_get_mask", "acmmp_fusion_stats",
     "acmmp_scan_create", "acmmp_scan_destroy", "acmmp_scan_last_error", "acmmp_scan_set_image",
     "acmmp_scan_set_shard", "acmmp_scan_set_sequential_geom", "acmmp_scan_num_levels", "acmmp_scan_begin_level",
-    "acmmp_scan_run_stage", "acmmp_scan_exchange", "acmmp_scan_view_size", "acmmp_scan_get_view",
+    "acmmp_scan_run_stage", "acmmp_scan_exchange", "acmmp_scan_view_size", "acmmp_scan_get_view", "acmmp_scan_view_device",
     "acmmp_scan_timing", "acmmp_scan_sync", "acmmp_scan_reset", "acmmp_scan_host_stats", "acmmp_scan_mark", "acmmp_scan_elapsed",
 ]
 
@@ -143,6 +145,17 @@ def load():
     lib.acmmp_scan_sync.argtypes = [vp]
     lib.acmmp_scan_reset.argtypes = [vp]
     lib.acmmp_scan_host_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.acmmp_fusion_create.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.POINTER(Camera), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.acmmp_fusion_destroy.argtypes = [vp]
+    lib.acmmp_fusion_destroy.restype = None
+    lib.acmmp_fusion_last_error.argtypes = [vp]
+    lib.acmmp_fusion_last_error.restype = C.c_char_p
+    lib.acmmp_fusion_set_view.argtypes = [vp, C.c_int, vp, vp, vp, vp, C.c_int]
+    lib.acmmp_fusion_run.argtypes = [vp, C.c_float, C.c_int, C.POINTER(C.c_int64)]
+    lib.acmmp_fusion_get_points.argtypes = [vp, vp, C.c_int64, C.POINTER(C.c_int64)]
+    lib.acmmp_fusion_get_mask.argtypes = [vp, C.c_int, vp]
+    lib.acmmp_fusion_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int32)]
+    lib.acmmp_scan_view_device.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     lib.acmmp_scan_count_ncc.argtypes = [vp, C.c_int]
     lib.acmmp_scan_ncc_count.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.acmmp_count_ncc.argtypes = [vp, C.c_int]

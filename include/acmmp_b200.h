@@ -298,6 +298,9 @@ int acmmp_scan_view_size(const acmmp_scan *s, int view, int *w, int *h);
 /* current maps of an owned view (.dmb payloads; depth = the last written depth
  * map); host pointers, any may be NULL. */
 int acmmp_scan_get_view(acmmp_scan *s, int view, float *depth, float *normal3, float *cost);
+/* the same maps as device pointers (valid until the next stage / level of the scan), e.g. to
+ * hand them to acmmp_fusion_set_view(..., on_device = 1) after acmmp_scan_sync */
+int acmmp_scan_view_device(acmmp_scan *s, int view, const float **d_depth, const float **d_normal3, const float **d_cost);
 /* device time spent in kernels, summed over all runs since the last call:
  * out_ms[0..3] = init, sweeps, tail, total; *runs = RunPatchMatch count;
  * *launches = kernel launches so far. */
@@ -316,6 +319,36 @@ int acmmp_scan_reset(acmmp_scan *s);
  * two recorded marks (waits for mark j). */
 int acmmp_scan_mark(acmmp_scan *s, int i);
 int acmmp_scan_elapsed(acmmp_scan *s, int i, int j, float *ms);
+
+/* ==== depth-map fusion =========================================================
+ * RunFusion (/root/reference/src/acmmp_definitions.cpp:828-1043) without the file
+ * I/O: the caller hands over, per view, the depth map the reference reads from
+ * depths[_geom].dmb, the normals of normals.dmb, the colour image rescaled to the
+ * depth map (RescaleImageAndCamera, :864) as 3 bytes per pixel in stored channel
+ * order (optional) and the optional depth mask (1 = ignore the pixel; the
+ * reference derives it as `png < 128`, :889).  `cams` are the cameras rescaled to
+ * the depth maps.  pair_offsets / pair_ids: the source views of every view as
+ * indices (CSR), like acmmp_scan_create.  Point order and the per-view used_list
+ * behaviour of the reference (:936) are preserved. */
+typedef struct acmmp_fusion acmmp_fusion;
+int acmmp_fusion_create(acmmp_fusion **out, int device, int n_views, const acmmp_camera *cams,
+                        const int32_t *pair_offsets, const int32_t *pair_ids);
+void acmmp_fusion_destroy(acmmp_fusion *f);
+const char *acmmp_fusion_last_error(const acmmp_fusion *f);
+/* host pointers, or device pointers on the fusion's device when on_device != 0 */
+int acmmp_fusion_set_view(acmmp_fusion *f, int view, const float *depth, const float *normal3,
+                          const uint8_t *color3, const uint8_t *mask, int on_device);
+/* consistency_scalar / con_num_thresh: main_ACMMP.cpp:17-18 (0.3, 1).  May be
+ * called again (the masks restart from the ones given to set_view). */
+int acmmp_fusion_run(acmmp_fusion *f, float consistency_scalar, int con_num_thresh, int64_t *num_points);
+/* points9: num_points x (x, y, z, nx, ny, nz, c0, c1, c2) floats in the order the
+ * reference appends them to the PLY (view by view, row-major); per_view_counts:
+ * n_views entries ("approved N pts", :1036).  Either may be NULL. */
+int acmmp_fusion_get_points(acmmp_fusion *f, float *points9, int64_t capacity, int64_t *per_view_counts);
+/* working mask of a view after the run (what later views see) */
+int acmmp_fusion_get_mask(acmmp_fusion *f, int view, uint8_t *mask);
+/* device ms of the last run: {score, greedy fixed point, compaction}; fixed-point rounds per view */
+int acmmp_fusion_stats(acmmp_fusion *f, double ms[3], int32_t *rounds_per_view);
 
 #ifdef __cplusplus
 }
