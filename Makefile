@@ -30,13 +30,32 @@ oracle/liboracle.so: $(wildcard oracle/*.c) $(wildcard oracle/*.h)
 
 # The reference's own kernels, compiled from where they lie (never copied into the
 # repo), sm_100 + the reference's flags; only built where /root/reference exists.
-ref: oracle/_ref/libacmmp_ref.so
+ref: oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so
 oracle/_ref/libacmmp_ref.so: oracle/ref_harness.cu $(wildcard oracle/ref_stub/opencv2/*.hpp)
 	@if [ -d $(REF) ]; then mkdir -p oracle/_ref && \
 	$(NVCC) -O3 --use_fast_math --maxrregcount=128 -std=c++14 -gencode arch=compute_100,code=sm_100 \
 	  -Ioracle/ref_stub -I$(REF) -Iinclude -Xcompiler -fPIC -shared -o $@ oracle/ref_harness.cu -lcudart ; \
 	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
 
+# The reference's HOST code (RunFusion + helpers: ACMMP.cpp, acmmp_definitions.cpp) against the
+# stand-in OpenCV.  Two builds: the reference's own flags (src/CMakeLists.txt:28, minus
+# -march=native so that the library also runs on the GPU box's CPU) and plain IEEE arithmetic
+# (-O2), against which the C restatement under oracle/ is bit-exact.
+CUDA_INC ?= /usr/local/cuda/include
+CUDA_LIB ?= /usr/local/cuda/lib64
+# the g++ on PATH: the image's $$CXX wrapper links libstdc++ statically, which breaks iostreams
+# inside a library that is dlopen()ed into python
+REF_CXX ?= $(shell command -v g++)
+REF_HOST_SRC := oracle/ref_host_harness.cpp $(wildcard oracle/ref_stub/opencv2/*.hpp)
+oracle/_ref/libacmmp_ref_host.so: $(REF_HOST_SRC)
+	@if [ -d $(REF) ]; then mkdir -p oracle/_ref && \
+	$(REF_CXX) -O3 -ffast-math -std=c++14 -fPIC -shared -w -Ioracle/ref_stub -I$(REF) -I$(CUDA_INC) -o $@ oracle/ref_host_harness.cpp -L$(CUDA_LIB) -lcudart ; \
+	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
+oracle/_ref/libacmmp_ref_host_ieee.so: $(REF_HOST_SRC)
+	@if [ -d $(REF) ]; then mkdir -p oracle/_ref && \
+	$(REF_CXX) -O2 -std=c++14 -fPIC -shared -w -Ioracle/ref_stub -I$(REF) -I$(CUDA_INC) -o $@ oracle/ref_host_harness.cpp -L$(CUDA_LIB) -lcudart ; \
+	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
+
 clean:
-	rm -f $(LIB) oracle/liboracle.so oracle/_ref/libacmmp_ref.so
+	rm -f $(LIB) build/fusion.o oracle/liboracle.so oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so
 .PHONY: all oracle ref clean

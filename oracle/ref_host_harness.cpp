@@ -1,0 +1,30 @@
+// ref_host_harness.cpp - parity comparator for the HOST side of the reference: its own
+// RunFusion (acmmp_definitions.cpp:828-1043) with ReadCamera / readDepthDmb / readNormalDmb /
+// RescaleImageAndCamera / Get3DPointonWorld / ProjectonCamera / GetAngle /
+// StoreColorPlyFileBinaryPointCloud (ACMMP.cpp), compiled from where the sources lie under
+// /root/reference/src (never copied into this repository) against the stand-in OpenCV of
+// oracle/ref_stub.  The test writes the reference's on-disk inputs (cams/*_cam.txt,
+// images/*.jpg as a raw container, 2333_*/depths_geom.dmb, normals.dmb), calls RunFusion and
+// reads ACMMP_model.ply back.
+//
+// TEST INFRASTRUCTURE ONLY.  Nothing under acmmp_b200/ links, loads or calls this file or its
+// output (oracle/_ref/libacmmp_ref_host.so).
+#include "ACMMP.cpp"
+#include "acmmp_definitions.cpp"
+
+// members defined in the reference's ACMMP.cu (device side; not part of this library, never called)
+void ACMMP::RunPatchMatch() {}
+void JBU::CudaRun() {}
+
+extern "C" int ref_host_run_fusion(const char *dense_folder, const char *out_folder, int n_views, const int *image_ids,
+                                   const int *pair_offsets, const int *pair_image_ids, int geom_consistency,
+                                   float consistency_scalar, int con_num_thresh) {
+    std::vector<Problem> problems(n_views);
+    for (int i = 0; i < n_views; ++i) {
+        problems[i].ref_image_id = image_ids[i];
+        for (int k = pair_offsets[i]; k < pair_offsets[i + 1]; ++k) problems[i].src_image_ids.push_back(pair_image_ids[k]);
+    }
+    std::string dense(dense_folder), out(out_folder);
+    RunFusion(dense, out, problems, geom_consistency != 0, consistency_scalar, con_num_thresh, std::string("/images"), std::string(" "));
+    return 0;
+}

@@ -8,6 +8,12 @@
  *
  * TEST INFRASTRUCTURE (see oracle.h).
  *
+ * Pinning: orc_fusion is checked against the reference's OWN RunFusion, compiled from
+ * where it lies (oracle/ref_host_harness.cpp -> oracle/_ref/libacmmp_ref_host*.so) and run
+ * on its own on-disk layout: bit-exact (points, order, normals, colours) against the IEEE
+ * build, identical accepted set against the -O3 -ffast-math build
+ * (tests/test_fusion_pinned.py).
+ *
  * Third-party arithmetic not under /root/reference: OpenCV (unpinned; Docker
  * image installs Ubuntu 18.04 libopencv-dev 3.2).  resize_linear restates the
  * published INTER_LINEAR algorithm for float images (source coordinate

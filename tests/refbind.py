@@ -162,3 +162,87 @@ def ref_jbu(image, depth):
     if rc != 0:
         raise RuntimeError("ref_jbu failed")
     return out
+
+
+# ---- the reference's HOST code (RunFusion) ---------------------------------------------
+_REF_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle", "_ref")
+REF_HOST_PATHS = {"reference_flags": os.path.join(_REF_DIR, "libacmmp_ref_host.so"),     # -O3 -ffast-math
+                  "ieee": os.path.join(_REF_DIR, "libacmmp_ref_host_ieee.so")}           # -O2
+_ref_host = {}
+
+
+def host_available():
+    return all(os.path.exists(p) for p in REF_HOST_PATHS.values())
+
+
+def _write_dmb(path, arr):
+    a = np.ascontiguousarray(arr, np.float32)
+    h, w = a.shape[:2]
+    nb = 1 if a.ndim == 2 else a.shape[2]
+    with open(path, "wb") as f:
+        np.array([1, h, w, nb], np.int32).tofile(f)     # writeDepthDmb / writeNormalDmb, ACMMP.cpp:294-380
+        a.tofile(f)
+
+
+def _write_cam(path, cam):
+    """cams/%08d_cam.txt as ReadCamera parses it (ACMMP.cpp:149-177)"""
+    R, t, K = cam.R[:], cam.t[:], cam.K[:]
+    with open(path, "w") as f:
+        f.write("extrinsic\n")
+        for i in range(3):
+            f.write("%.9g %.9g %.9g %.9g\n" % (R[3 * i], R[3 * i + 1], R[3 * i + 2], t[i]))
+        f.write("0 0 0 1\n\nintrinsic\n")
+        for i in range(3):
+            f.write("%.9g %.9g %.9g\n" % (K[3 * i], K[3 * i + 1], K[3 * i + 2]))
+        f.write("\n%.9g 1 192 %.9g\n" % (cam.depth_min, cam.depth_max))
+
+
+def host_fusion(workdir, cams, depths, normals, colors, pairs, consistency_scalar=0.3, con_num_thresh=1, geom=True,
+                build="reference_flags", timing=None):
+    """The reference's own RunFusion on its own on-disk layout under `workdir`; returns the
+    points of ACMMP_model.ply as (N, 9) floats: x y z nx ny nz + the three colour bytes in the
+    order they sit in the file."""
+    if build not in _ref_host:
+        lib = C.CDLL(REF_HOST_PATHS[build])
+        lib.ref_host_run_fusion.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                            C.POINTER(C.c_int), C.c_int, C.c_float, C.c_int]
+        _ref_host[build] = lib
+    n = len(cams)
+    dense = os.path.join(workdir, "dense")
+    out = os.path.join(workdir, "dense", "ACMMP")
+    os.makedirs(os.path.join(dense, "images"), exist_ok=True)
+    os.makedirs(os.path.join(dense, "cams"), exist_ok=True)
+    for i in range(n):
+        h, w = depths[i].shape
+        col = np.zeros((h, w, 3), np.uint8) if colors is None else np.ascontiguousarray(colors[i], np.uint8)
+        with open(os.path.join(dense, "images", "%08d.jpg" % i), "wb") as f:      # raw container, see oracle/ref_stub
+            f.write(b"ACMRAW1 %d %d 3\n" % (h, w))
+            f.write(col.tobytes())
+        _write_cam(os.path.join(dense, "cams", "%08d_cam.txt" % i), cams[i])
+        vd = os.path.join(out, "2333_%08d" % i)
+        os.makedirs(vd, exist_ok=True)
+        _write_dmb(os.path.join(vd, "depths_geom.dmb" if geom else "depths.dmb"), depths[i])
+        _write_dmb(os.path.join(vd, "normals.dmb"), normals[i])
+    ids = (C.c_int * n)(*range(n))
+    offs = [0]
+    flat = []
+    for p in pairs:
+        flat += list(p)
+        offs.append(len(flat))
+    import time
+    t0 = time.time()
+    rc = _ref_host[build].ref_host_run_fusion(dense.encode(), out.encode(), n, ids, (C.c_int * (n + 1))(*offs),
+                                              (C.c_int * max(1, len(flat)))(*flat), int(geom), float(consistency_scalar), int(con_num_thresh))
+    if timing is not None:
+        timing["run_fusion_s"] = time.time() - t0     # includes its file reads and the PLY write, as in the reference
+    assert rc == 0
+    with open(os.path.join(out, "ACMMP_model.ply"), "rb") as f:
+        blob = f.read()
+    end = blob.index(b"end_header\n") + len(b"end_header\n")
+    header = blob[:end].decode()
+    count = int([l for l in header.splitlines() if l.startswith("element vertex")][0].split()[-1])
+    rec = np.frombuffer(blob[end:end + 27 * count], dtype=np.dtype([("f", "<f4", 6), ("c", "u1", 3)]))
+    pts = np.zeros((count, 9), np.float32)
+    pts[:, :6] = rec["f"]
+    pts[:, 6:] = rec["c"]
+    return pts

@@ -19,25 +19,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 from acmmp_b200 import host  # noqa: E402
 from acmmp_b200.scene import make_scene  # noqa: E402
-
-
-def noisy_maps(sc, seed, noise=0.002, holes=0.02, outliers=0.03):
-    """depth maps like PatchMatch leaves them: small noise, some holes (0) and gross errors;
-    world-frame normals around one direction with a few degrees of scatter"""
-    rng = np.random.default_rng(seed)
-    depths, normals, colors = [], [], []
-    for d in sc["depths"]:
-        h, w = d.shape
-        x = d * (1.0 + noise * rng.standard_normal((h, w)))
-        bad = rng.random((h, w)) < outliers
-        x[bad] *= rng.uniform(0.8, 1.2, size=int(bad.sum()))
-        x[rng.random((h, w)) < holes] = 0.0
-        depths.append(np.ascontiguousarray(x, np.float32))
-        n = rng.normal(size=(h, w, 3)) * 0.06 + np.array([0.0, 0.0, 1.0])
-        n /= np.linalg.norm(n, axis=-1, keepdims=True)
-        normals.append(np.ascontiguousarray(n, np.float32))
-        colors.append(rng.integers(0, 256, size=(h, w, 3), dtype=np.uint8))
-    return depths, normals, colors
+from fusion_inputs import noisy_maps  # noqa: E402
 
 
 def point_keys(pts):
