@@ -259,6 +259,31 @@ def run_ours(args):
         "clocks": clocks.summary(),
         "exchanges_per_step": exchanges_per_step,
     }
+    if world == 1:
+        # next row of the scope table: depth-map fusion of this scan's final maps on the
+        # device, beside the CPU restatement of the reference's RunFusion on the same maps (outside
+        # the timed region; not part of `value`)
+        scan.reset()
+        scan.run_all(seed=1234, exchange=exchange)
+        scan.sync()
+        fus = host.Fusion(sc["cams"], sc["pairs"], device=local)
+        for v in range(n):
+            d_, n_, _ = scan.view_device(v)
+            fus.set_view(v, d_, n_, on_device=True)
+        fus.run(0.3, 1)
+        t0 = time.time()
+        npts = fus.run(0.3, 1)
+        fwall = time.time() - t0
+        fst = fus.stats()
+        line["fusion"] = {"points": int(npts), "ms": fwall * 1e3, "device_ms": fst["score_ms"] + fst["greedy_ms"] + fst["emit_ms"],
+                          "fixed_point_rounds_max": max(fst["rounds"]), "consistency_scalar": 0.3, "num_consistent_thresh": 1}
+        if not args.no_cpu_baseline:
+            import oraclebind as ob
+            maps = [scan.get_view(v, want_cost=False) for v in range(n)]
+            t0 = time.time()
+            cnt = ob.fusion(sc["cams"], [m[0] for m in maps], [m[1] for m in maps], sc["pairs"], 0.3, 1)
+            line["fusion"].update({"cpu_port_s": time.time() - t0, "cpu_port_points": int(cnt), "cpu_cores": 1})
+        fus.close()
     if rank == 0 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args, sc, hpv)
     if rank == 0:
