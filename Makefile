@@ -10,8 +10,22 @@ NVFLAGS   := -O3 --use_fast_math -std=c++17 $(ARCH) -lineinfo -Xcompiler -fPIC
 CSRC      := acmmp_b200/csrc
 LIB       := acmmp_b200/libacmmp_b200.so
 REF       := /root/reference/src
+CUDA_INC  ?= /usr/local/cuda/include
+CUDA_LIB  ?= /usr/local/cuda/lib64
+# the g++ on PATH: the image's $$CXX wrapper links libstdc++ statically, which breaks iostreams
+# inside a library that is dlopen()ed into python
+REF_CXX   ?= $(shell command -v g++)
 
-all: $(LIB) oracle
+all: $(LIB) oracle cli
+
+# command line with the reference's flags and file layout (cli/acmmp_main.cpp) over the C ABI
+cli: build/acmmp_main build/io_selftest
+build/io_selftest: cli/io_selftest.cpp $(wildcard acmmp_b200/host/*.hpp) include/acmmp_b200.h
+	@mkdir -p build
+	$(REF_CXX) -O2 -std=c++17 -Wall -o $@ cli/io_selftest.cpp
+build/acmmp_main: cli/acmmp_main.cpp $(wildcard acmmp_b200/host/*.hpp) include/acmmp_b200.h $(LIB)
+	@mkdir -p build
+	$(REF_CXX) -O2 -std=c++17 -Wall -o $@ cli/acmmp_main.cpp -Lacmmp_b200 -lacmmp_b200 -Wl,-rpath,'$$ORIGIN/../acmmp_b200' -L$(CUDA_LIB) -lcudart
 
 # fusion.cu restates host code of the reference (IEEE float / double): no fast math, no contraction
 FUSIONFLAGS := -O3 -std=c++17 $(ARCH) -lineinfo -fmad=false -Xcompiler -fPIC
@@ -41,11 +55,6 @@ oracle/_ref/libacmmp_ref.so: oracle/ref_harness.cu $(wildcard oracle/ref_stub/op
 # stand-in OpenCV.  Two builds: the reference's own flags (src/CMakeLists.txt:28, minus
 # -march=native so that the library also runs on the GPU box's CPU) and plain IEEE arithmetic
 # (-O2), against which the C restatement under oracle/ is bit-exact.
-CUDA_INC ?= /usr/local/cuda/include
-CUDA_LIB ?= /usr/local/cuda/lib64
-# the g++ on PATH: the image's $$CXX wrapper links libstdc++ statically, which breaks iostreams
-# inside a library that is dlopen()ed into python
-REF_CXX ?= $(shell command -v g++)
 REF_HOST_SRC := oracle/ref_host_harness.cpp $(wildcard oracle/ref_stub/opencv2/*.hpp)
 oracle/_ref/libacmmp_ref_host.so: $(REF_HOST_SRC)
 	@if [ -d $(REF) ]; then mkdir -p oracle/_ref && \
@@ -58,4 +67,4 @@ oracle/_ref/libacmmp_ref_host_ieee.so: $(REF_HOST_SRC)
 
 clean:
 	rm -f $(LIB) build/fusion.o oracle/liboracle.so oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so
-.PHONY: all oracle ref clean
+.PHONY: all oracle ref cli clean

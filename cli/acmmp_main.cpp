@@ -1,0 +1,204 @@
+// acmmp_main.cpp - command line of the B200 path with the reference's flags and file layout
+// (main_ACMMP.cpp:9-199): reads <dense_folder>/pair.txt, cams/%08d_cam.txt, images/%08d.*,
+// runs the multi-scale schedule (photometric + planar prior, geom x2 per scale) resident on
+// the device, writes <dense_folder><output_dir>/2333_%08d/{depths,depths_geom,normals,costs}.dmb
+// and fuses into ACMMP_model.ply.  Hand-rolled flag parser (Boost is not in this image).
+// Not supported (out of scope): --prior, --multi_fusion, --force_fusion,
+// --single_match_penalty - they need the external prior package that is not in the reference tree.
+#include <sys/stat.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../acmmp_b200/host/acmmp.hpp"
+
+using namespace acmmp_b200;
+
+static std::string id_name(int id, const char *suffix) {
+    char buf[64];
+    snprintf(buf, sizeof buf, "%08d%s", id, suffix);
+    return buf;
+}
+
+static bool find_image(const std::string &folder, int id, Map<uint8_t> &im, std::string &err) {
+    for (const char *ext : {".jpg", ".pgm", ".ppm", ".raw"}) {   // the tests keep the reference's .jpg name for the raw container
+        std::string e;
+        if (ReadImage(folder + "/" + id_name(id, ext), im, &e)) return true;
+        if (!e.empty() && e.find("cannot open") == std::string::npos) err = e;
+    }
+    if (err.empty()) err = "no image for id " + std::to_string(id) + " under " + folder;
+    return false;
+}
+
+int main(int argc, char **argv) {
+    std::string dense_folder, output_dir = "/ACMMP", mask_dir = " ", image_dir = "/images";
+    float consistency_scalar = 0.3f;
+    int num_consistent_thresh = 1, device = 0;
+    unsigned long long seed = 0;
+    bool fuse = true;
+    for (int i = 1; i < argc; ++i) {
+        const std::string a = argv[i];
+        auto value = [&](const char *name) -> const char * {
+            if (i + 1 >= argc) {
+                fprintf(stderr, "missing value for %s\n", name);
+                exit(EXIT_FAILURE);
+            }
+            return argv[++i];
+        };
+        if (a == "-h" || a == "--help") {
+            printf("usage: acmmp_main <dense_folder> [--output_dir /ACMMP] [-f|--fuse_thresh 0.3] [--num_consistent_thresh 1]\n"
+                   "                  [--mask_dir DIR] [--image_override DIR] [--device 0] [--seed N] [--no_fusion]\n");
+            return 1;
+        } else if (a == "--dense_folder") dense_folder = value("--dense_folder");
+        else if (a == "--output_dir") output_dir = value("--output_dir");
+        else if (a == "-f" || a == "--fuse_thresh") consistency_scalar = (float)atof(value("--fuse_thresh"));
+        else if (a == "--num_consistent_thresh") num_consistent_thresh = atoi(value("--num_consistent_thresh"));
+        else if (a == "--mask_dir") mask_dir = value("--mask_dir");
+        else if (a == "--image_override") image_dir = value("--image_override");
+        else if (a == "--device") device = atoi(value("--device"));
+        else if (a == "--seed") seed = strtoull(value("--seed"), nullptr, 10);
+        else if (a == "--no_fusion") fuse = false;
+        else if (a == "-p" || a == "--prior" || a == "--multi_fusion" || a == "--force_fusion" || a == "--single_match_penalty") {
+            fprintf(stderr, "%s: prior-aware modes need the external prior package; not supported\n", a.c_str());
+            return EXIT_FAILURE;
+        } else if (a[0] != '-') dense_folder = a;
+        else {
+            fprintf(stderr, "unknown option %s\n", a.c_str());
+            return EXIT_FAILURE;
+        }
+    }
+    if (dense_folder.empty()) {
+        fprintf(stderr, "no dense_folder given\n");
+        return EXIT_FAILURE;
+    }
+    try {
+        std::vector<Problem> problems;
+        if (!GenerateSampleList(dense_folder, problems) || problems.empty()) {
+            fprintf(stderr, "cannot read %s/pair.txt\n", dense_folder.c_str());
+            return EXIT_FAILURE;
+        }
+        const int n = (int)problems.size();
+        printf("There are %d problems needed to be processed!\n", n);
+        std::map<int, int> image_id_2_index;
+        for (int i = 0; i < n; ++i) image_id_2_index[problems[i].ref_image_id] = i;
+        std::vector<acmmp_camera> cams(n);
+        std::vector<Map<uint8_t>> images(n);
+        std::vector<std::vector<int>> pairs(n);
+        for (int i = 0; i < n; ++i) {
+            const int id = problems[i].ref_image_id;
+            if (!ReadCamera(dense_folder + "/cams/" + id_name(id, "_cam.txt"), cams[i])) {
+                fprintf(stderr, "cannot read camera of image %d\n", id);
+                return EXIT_FAILURE;
+            }
+            std::string err;
+            if (!find_image(dense_folder + "/images", id, images[i], err)) {
+                fprintf(stderr, "%s\n", err.c_str());
+                return EXIT_FAILURE;
+            }
+            cams[i].width = images[i].cols;
+            cams[i].height = images[i].rows;
+            for (int sid : problems[i].src_image_ids) {
+                auto it = image_id_2_index.find(sid);
+                if (it == image_id_2_index.end()) {
+                    fprintf(stderr, "pair.txt: source %d of image %d is not a reference image\n", sid, id);
+                    return EXIT_FAILURE;
+                }
+                pairs[i].push_back(it->second);
+            }
+        }
+        const std::string output_folder = dense_folder + output_dir;
+        mkdir(output_folder.c_str(), 0777);
+
+        Scan scan(cams, pairs, device);
+        for (int i = 0; i < n; ++i) scan.SetImage(i, ToGrayFloat(images[i]));
+        std::vector<Map<float>> photo_depth(n);
+        const int levels = scan.NumLevels();
+        for (int level = 0; level < levels; ++level) {
+            printf("Scale: %d\n", levels - 1 - level);
+            scan.BeginLevel(level);
+            for (int stage = ACMMP_STAGE_PHOTO; stage <= ACMMP_STAGE_GEOM1; ++stage) {
+                scan.RunStage(stage, seed);
+                if (level == levels - 1 && stage == ACMMP_STAGE_PHOTO)   // depths.dmb = the photometric + planar-prior result
+                    for (int i = 0; i < n; ++i) scan.GetView(i, &photo_depth[i], nullptr, nullptr);
+            }
+        }
+        scan.Sync();
+        // acmmp_definitions.cpp:392-401: one folder per reference image
+        std::vector<acmmp_camera> cams_out(n);
+        for (int i = 0; i < n; ++i) {
+            const std::string folder = output_folder + "/2333_" + id_name(problems[i].ref_image_id, "");
+            mkdir(folder.c_str(), 0777);
+            Map<float> depth, normal, cost;
+            scan.GetView(i, &depth, &normal, &cost);
+            if (writeDepthDmb(folder + "/depths.dmb", photo_depth[i]) || writeDepthDmb(folder + "/depths_geom.dmb", depth) ||
+                writeNormalDmb(folder + "/normals.dmb", normal) || writeDepthDmb(folder + "/costs.dmb", cost)) {
+                fprintf(stderr, "cannot write maps under %s\n", folder.c_str());
+                return EXIT_FAILURE;
+            }
+            // RescaleImageAndCamera (ACMMP.cpp:179-203): camera at the size of the depth map
+            cams_out[i] = cams[i];
+            const float sx = depth.cols / (float)cams[i].width, sy = depth.rows / (float)cams[i].height;
+            if (depth.cols != cams[i].width || depth.rows != cams[i].height) {
+                cams_out[i].K[0] *= sx; cams_out[i].K[2] *= sx; cams_out[i].K[4] *= sy; cams_out[i].K[5] *= sy;
+                cams_out[i].width = depth.cols;
+                cams_out[i].height = depth.rows;
+            }
+        }
+        printf("depth maps written to %s\n", output_folder.c_str());
+        if (fuse) {
+            Fusion fusion(cams_out, pairs, device);
+            for (int i = 0; i < n; ++i) {
+                Map<uint8_t> color = images[i];
+                if (image_dir != "/images") {
+                    std::string err;
+                    if (!find_image(dense_folder + image_dir, problems[i].ref_image_id, color, err)) {
+                        fprintf(stderr, "%s\n", err.c_str());
+                        return EXIT_FAILURE;
+                    }
+                }
+                if (color.cols != cams_out[i].width || color.rows != cams_out[i].height) {
+                    fprintf(stderr, "image %d: colour image size differs from the depth map (resize not built in)\n", problems[i].ref_image_id);
+                    return EXIT_FAILURE;
+                }
+                if (color.channels == 1) {   // grey input: replicate like imread(IMREAD_COLOR)
+                    Map<uint8_t> c3(color.rows, color.cols, 3);
+                    for (size_t k = 0; k < (size_t)color.rows * color.cols; ++k) c3.data[3 * k] = c3.data[3 * k + 1] = c3.data[3 * k + 2] = color.data[k];
+                    color = c3;
+                }
+                std::vector<uint8_t> mask;
+                if (mask_dir != " ") {   // acmmp_definitions.cpp:870-895: mask = png < 128
+                    Map<uint8_t> m;
+                    std::string err;
+                    if (!find_image(dense_folder + "/" + mask_dir, problems[i].ref_image_id, m, err) || m.cols != cams_out[i].width || m.rows != cams_out[i].height) {
+                        fprintf(stderr, "mask of image %d missing or of the wrong size\n", problems[i].ref_image_id);
+                        return EXIT_FAILURE;
+                    }
+                    mask.resize((size_t)m.rows * m.cols);
+                    for (size_t k = 0; k < mask.size(); ++k) mask[k] = m.data[k * m.channels] < 128 ? 1 : 0;
+                }
+                // colour and mask come from the host, so the maps take the same way (one flag per call)
+                Map<float> hd, hn;
+                scan.GetView(i, &hd, &hn, nullptr);
+                fusion.SetView(i, hd.data.data(), hn.data.data(), color.data.data(), mask.empty() ? nullptr : mask.data(), false);
+            }
+            const int64_t count = fusion.Run(consistency_scalar, num_consistent_thresh);
+            std::vector<float> pts;
+            std::vector<int64_t> per_view;
+            fusion.GetPoints(pts, per_view, count, n);
+            for (int i = 0; i < n; ++i) printf("Fusing image %08d... approved %lld pts\n", i, (long long)per_view[i]);
+            if (!StoreColorPlyFileBinaryPointCloud(output_folder + "/ACMMP_model.ply", pts.data(), (size_t)count)) {
+                fprintf(stderr, "cannot write the PLY\n");
+                return EXIT_FAILURE;
+            }
+            printf("store 3D points to ply file: %lld points\n", (long long)count);
+        }
+    } catch (const std::exception &e) {
+        fprintf(stderr, "%s\n", e.what());   // the reference: CudaSafeCall prints and exit(EXIT_FAILURE)
+        return EXIT_FAILURE;
+    }
+    return 0;
+}

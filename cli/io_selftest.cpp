@@ -1,0 +1,53 @@
+// io_selftest.cpp - exercises acmmp_b200/host/io.hpp from the CPU test-suite (tests/test_host_io.py):
+//   io_selftest <dir>   reads <dir>/pair.txt, <dir>/cams/00000000_cam.txt, <dir>/in.dmb, <dir>/img.ppm, <dir>/points.bin
+//                       writes <dir>/out.dmb, <dir>/gray.dmb, <dir>/out.ply and prints what it parsed as key=value lines
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+#include <vector>
+
+#include "../acmmp_b200/host/io.hpp"
+
+using namespace acmmp_b200;
+
+int main(int argc, char **argv) {
+    if (argc < 2) return 2;
+    const std::string dir = argv[1];
+    std::vector<Problem> problems;
+    if (!GenerateSampleList(dir, problems)) return 3;
+    printf("problems=%zu\n", problems.size());
+    for (const auto &p : problems) {
+        printf("ref=%d src=", p.ref_image_id);
+        for (int s : p.src_image_ids) printf("%d,", s);
+        printf("\n");
+    }
+    acmmp_camera cam;
+    if (!ReadCamera(dir + "/cams/00000000_cam.txt", cam)) return 4;
+    printf("K=");
+    for (float v : cam.K) printf("%.9g,", v);
+    printf("\nR=");
+    for (float v : cam.R) printf("%.9g,", v);
+    printf("\nt=%.9g,%.9g,%.9g\ndepth=%.9g,%.9g\n", cam.t[0], cam.t[1], cam.t[2], cam.depth_min, cam.depth_max);
+    Map<float> m;
+    if (readDmb(dir + "/in.dmb", m)) return 5;
+    printf("dmb=%d,%d,%d\n", m.rows, m.cols, m.channels);
+    if (writeDmb(dir + "/out.dmb", m.data.data(), m.rows, m.cols, m.channels)) return 6;
+    Map<uint8_t> im;
+    std::string err;
+    if (!ReadImage(dir + "/img.ppm", im, &err)) {
+        fprintf(stderr, "%s\n", err.c_str());
+        return 7;
+    }
+    printf("image=%d,%d,%d\n", im.rows, im.cols, im.channels);
+    if (writeDepthDmb(dir + "/gray.dmb", ToGrayFloat(im))) return 8;
+    FILE *f = fopen((dir + "/points.bin").c_str(), "rb");
+    if (!f) return 9;
+    std::vector<float> pts;
+    float rec[9];
+    while (fread(rec, sizeof(float), 9, f) == 9) pts.insert(pts.end(), rec, rec + 9);
+    fclose(f);
+    if (!StoreColorPlyFileBinaryPointCloud(dir + "/out.ply", pts.data(), pts.size() / 9)) return 10;
+    printf("points=%zu\n", pts.size() / 9);
+    if (ReadImage(dir + "/pair.txt", im, &err)) return 11;   // must be rejected
+    return 0;
+}

@@ -1,0 +1,106 @@
+"""The C++ command line (cli/acmmp_main.cpp, build/acmmp_main) on the reference's on-disk layout:
+pair.txt, cams/*_cam.txt, images/*  ->  2333_*/{depths,depths_geom,normals,costs}.dmb + ACMMP_model.ply;
+the files it writes are then fed to the reference's OWN RunFusion.  pytest -m gpu."""
+import os
+import shutil
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+if not torch.cuda.is_available():
+    pytest.skip("no CUDA device", allow_module_level=True)
+
+import refbind  # noqa: E402
+from acmmp_b200.scene import make_scene  # noqa: E402
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "build", "acmmp_main")
+
+
+def read_dmb(path):
+    hdr = np.fromfile(path, np.int32, 4)
+    assert hdr[0] == 1
+    a = np.fromfile(path, np.float32, offset=16)
+    return a.reshape(hdr[1], hdr[2]) if hdr[3] == 1 else a.reshape(hdr[1], hdr[2], hdr[3])
+
+
+def read_ply(path):
+    blob = open(path, "rb").read()
+    end = blob.index(b"end_header\n") + 11
+    n = int([l for l in blob[:end].decode().splitlines() if l.startswith("element vertex")][0].split()[-1])
+    rec = np.frombuffer(blob[end:end + 27 * n], dtype=np.dtype([("f", "<f4", 6), ("c", "u1", 3)]))
+    return rec["f"].copy(), rec["c"].copy()
+
+
+@pytest.fixture(scope="module")
+def cli_run(tmp_path_factory):
+    if not os.path.exists(EXE):
+        pytest.skip("build/acmmp_main not built (make cli)")
+    sc = make_scene(5, 320, 240, 4, seed=6)
+    dense = str(tmp_path_factory.mktemp("cli") / "dense")
+    os.makedirs(os.path.join(dense, "images"))
+    os.makedirs(os.path.join(dense, "cams"))
+    n = 5
+    ids = [10 * i + 3 for i in range(n)]                      # image ids are not indices
+    with open(os.path.join(dense, "pair.txt"), "w") as f:
+        f.write("%d\n" % n)
+        for i in range(n):
+            f.write("%d\n%d " % (ids[i], len(sc["pairs"][i])) + " ".join("%d 1.0" % ids[j] for j in sc["pairs"][i]) + "\n")
+    for i in range(n):
+        img = np.clip(np.rint(sc["images"][i]), 0, 255).astype(np.uint8)
+        with open(os.path.join(dense, "images", "%08d.jpg" % ids[i]), "wb") as f:   # raw container under the reference's name
+            f.write(b"ACMRAW1 %d %d 1\n" % img.shape + img.tobytes())
+        refbind._write_cam(os.path.join(dense, "cams", "%08d_cam.txt" % ids[i]), sc["cams"][i])
+    out = subprocess.run([EXE, dense, "--seed", "5"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    return sc, dense, ids, out.stdout
+
+
+def test_cli_writes_the_reference_layout(cli_run):
+    sc, dense, ids, stdout = cli_run
+    n = len(ids)
+    outdir = os.path.join(dense, "ACMMP")
+    for i in range(n):
+        folder = os.path.join(outdir, "2333_%08d" % ids[i])
+        depth = read_dmb(os.path.join(folder, "depths_geom.dmb"))
+        normal = read_dmb(os.path.join(folder, "normals.dmb"))
+        cost = read_dmb(os.path.join(folder, "costs.dmb"))
+        photo = read_dmb(os.path.join(folder, "depths.dmb"))
+        assert depth.shape == (240, 320) and normal.shape == (240, 320, 3) and cost.shape == (240, 320) and photo.shape == (240, 320)
+        gt = sc["depths"][i]
+        assert (np.abs(depth - gt)[8:-8, 8:-8] / gt[8:-8, 8:-8] < 0.01).mean() >= 0.9
+        assert np.abs(np.linalg.norm(normal, axis=-1) - 1).max() < 1e-3
+    xyz_n, col = read_ply(os.path.join(outdir, "ACMMP_model.ply"))
+    assert len(xyz_n) > 50000 and np.isfinite(xyz_n).all()
+    assert "approved" in stdout
+
+
+@pytest.mark.skipif(not refbind.host_available(), reason="oracle/_ref/libacmmp_ref_host*.so not built")
+def test_reference_runfusion_reads_the_cli_output(cli_run):
+    """the reference's own RunFusion on the files the CLI wrote (same ids, same layout)"""
+    sc, dense, ids, _ = cli_run
+    n = len(ids)
+    outdir = os.path.join(dense, "ACMMP")
+    xyz_n, col = read_ply(os.path.join(outdir, "ACMMP_model.ply"))
+    shutil.copy(os.path.join(outdir, "ACMMP_model.ply"), os.path.join(outdir, "ours.ply"))
+    import ctypes as C
+    lib = C.CDLL(refbind.REF_HOST_PATHS["ieee"])
+    lib.ref_host_run_fusion.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                        C.c_int, C.c_float, C.c_int]
+    offs, flat = [0], []
+    for p in sc["pairs"]:
+        flat += [ids[j] for j in p]
+        offs.append(len(flat))
+    rc = lib.ref_host_run_fusion(dense.encode(), outdir.encode(), n, (C.c_int * n)(*ids), (C.c_int * (n + 1))(*offs),
+                                 (C.c_int * len(flat))(*flat), 1, 0.3, 1)
+    assert rc == 0
+    ref_xyz_n, ref_col = read_ply(os.path.join(outdir, "ACMMP_model.ply"))
+    assert abs(len(ref_xyz_n) - len(xyz_n)) <= max(1, int(1e-3 * len(ref_xyz_n))), (len(ref_xyz_n), len(xyz_n))
+    if len(ref_xyz_n) == len(xyz_n):
+        same = (ref_xyz_n.view(np.uint32) == xyz_n.view(np.uint32)).all(1).mean()
+        assert same >= 0.999, same
+        assert (ref_col == col).all()

@@ -1,0 +1,65 @@
+"""C++ host I/O (acmmp_b200/host/io.hpp) on the reference's file formats: cam text, pair.txt,
+.dmb, PGM/PPM, binary PLY - through build/io_selftest.  CPU only."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import refbind
+from acmmp_b200 import lib as L
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "build", "io_selftest")
+
+pytestmark = pytest.mark.skipif(not os.path.exists(EXE), reason="build/io_selftest not built (make cli)")
+
+
+def test_formats_round_trip(tmp_path):
+    d = str(tmp_path)
+    rng = np.random.default_rng(0)
+    with open(os.path.join(d, "pair.txt"), "w") as f:          # select_dtu_cams.py:28-35 layout
+        f.write("3\n0\n3 1 2.5 2 1.0 7 0.0\n1\n2 0 1.0 2 1.0\n2\n1 0 -1\n")
+    os.makedirs(os.path.join(d, "cams"))
+    K = [2892.33, 0, 823.205, 0, 2883.18, 619.07, 0, 0, 1]
+    R = np.linalg.qr(rng.normal(size=(3, 3)))[0].astype(np.float32).reshape(9)
+    cam = L.Camera.make(K, R, [1.5, -2.25, 600.125], 1600, 1200, 425.0, 935.0)
+    refbind._write_cam(os.path.join(d, "cams", "00000000_cam.txt"), cam)
+    m = rng.normal(size=(7, 5, 3)).astype(np.float32)
+    refbind._write_dmb(os.path.join(d, "in.dmb"), m)
+    img = rng.integers(0, 256, size=(6, 9, 3), dtype=np.uint8)   # RGB in the PPM
+    with open(os.path.join(d, "img.ppm"), "wb") as f:
+        f.write(b"P6\n9 6\n255\n" + img.tobytes())
+    pts = rng.normal(size=(11, 9)).astype(np.float32)
+    pts[:, 6:] = rng.integers(0, 256, size=(11, 3))
+    pts[3, 0] = np.inf
+    pts.tofile(os.path.join(d, "points.bin"))
+    out = subprocess.run([EXE, d], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    kv = dict(l.split("=", 1) for l in out.stdout.splitlines() if "=" in l and not l.startswith("ref="))
+    refs = [l for l in out.stdout.splitlines() if l.startswith("ref=")]
+    assert kv["problems"] == "3"
+    assert refs == ["ref=0 src=1,2,", "ref=1 src=0,2,", "ref=2 src="]           # scores <= 0 dropped
+    assert np.array_equal(np.float32([float(x) for x in kv["K"].strip(",").split(",")]), np.float32(K))
+    assert np.array_equal(np.float32([float(x) for x in kv["R"].strip(",").split(",")]), R)
+    assert kv["t"] == "1.5,-2.25,600.125" and kv["depth"] == "425,935"
+    assert kv["dmb"] == "7,5,3"
+    assert open(os.path.join(d, "out.dmb"), "rb").read() == open(os.path.join(d, "in.dmb"), "rb").read()
+    assert kv["image"] == "6,9,3"
+    gray = np.fromfile(os.path.join(d, "gray.dmb"), np.float32, offset=16).reshape(6, 9)
+    b, g, r = img[..., 2].astype(np.int64), img[..., 1].astype(np.int64), img[..., 0].astype(np.int64)
+    assert np.array_equal(gray, ((b * 1868 + g * 9617 + r * 4899 + 8192) >> 14).astype(np.float32))
+    try:
+        import cv2
+        assert np.abs(gray - cv2.cvtColor(img, cv2.COLOR_RGB2GRAY).astype(np.float32)).max() <= 1   # OpenCV's own rounding
+    except ImportError:
+        pass
+    blob = open(os.path.join(d, "out.ply"), "rb").read()
+    end = blob.index(b"end_header\n") + 11
+    assert b"element vertex 11\n" in blob[:end] and b"format binary_little_endian 1.0" in blob[:end]
+    rec = np.frombuffer(blob[end:], dtype=np.dtype([("f", "<f4", 6), ("c", "u1", 3)]))
+    assert len(rec) == 11
+    exp = pts.copy()
+    exp[3, :3] = 0                                                     # non-finite coordinates are zeroed (ACMMP.cpp:414-418)
+    assert np.array_equal(rec["f"], exp[:, :6])
+    assert np.array_equal(rec["c"], exp[:, [8, 7, 6]].astype(np.uint8))  # red, green, blue = c2, c1, c0
