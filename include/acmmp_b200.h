@@ -6,9 +6,9 @@
  * /root/reference/src/ACMMP.h:58-124,142-160,18-20 and driven by
  * ProcessProblem / JointBilateralUpsampling
  * (/root/reference/src/acmmp_definitions.cpp:245-440).  Every entry point below
- * names the reference member it replaces.  The C++ host class in
- * acmmp_b200/host/acmmp.hpp and the Python mirror in acmmp_b200/host.py are
- * thin callers of this ABI.  No torch / C++ types cross this boundary.
+ * names the reference member it replaces.  The C++ host classes in
+ * acmmp_b200/host/acmmp.hpp (command line: cli/acmmp_main.cpp) and the Python
+ * mirror in acmmp_b200/host.py are thin callers of this ABI.  No torch / C++ types cross this boundary.
  *
  * Conventions: every function returns 0 on success and a negative acmmp_status
  * on failure (the reference prints and exit()s, ACMMP.cpp:67-100; here the
