@@ -34,8 +34,8 @@ build/fusion.o: $(CSRC)/fusion.cu include/acmmp_b200.h
 	@mkdir -p build
 	$(NVCC) $(FUSIONFLAGS) -c -o $@ $(CSRC)/fusion.cu
 
-$(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp build/fusion.o $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp build/fusion.o -lcudart
+$(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o -lnvjpeg_static -lculibos -lcudart
 
 oracle: oracle/liboracle.so
 

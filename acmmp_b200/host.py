@@ -471,3 +471,18 @@ def RunFusion(cams, pairs, depths, normals, colors=None, masks=None, consistency
         return f.points()
     finally:
         f.close()
+
+
+def decode_jpeg(data, color=False, device=0):
+    """JPEG bytes -> (H, W) uint8 luma, or (H, W, 3) uint8 BGR with color=True, decoded on the
+    device by nvJPEG: what cv::imread(IMREAD_GRAYSCALE / IMREAD_COLOR) hands the reference."""
+    lib = L.load()
+    buf = np.frombuffer(bytes(data), np.uint8)
+    w, h = C.c_int(), C.c_int()
+    ptr = C.c_void_p(buf.ctypes.data)
+    if lib.acmmp_decode_jpeg(device, ptr, buf.size, int(color), None, 0, C.byref(w), C.byref(h)) != 0:
+        raise L.AcmmpError(lib.acmmp_jpeg_last_error().decode())
+    out = np.empty((h.value, w.value, 3) if color else (h.value, w.value), np.uint8)
+    if lib.acmmp_decode_jpeg(device, ptr, buf.size, int(color), C.c_void_p(out.ctypes.data), out.nbytes, C.byref(w), C.byref(h)) != 0:
+        raise L.AcmmpError(lib.acmmp_jpeg_last_error().decode())
+    return out

@@ -101,13 +101,42 @@ inline int readNormalDmb(const std::string &p, Map<float> &normal) { return read
 
 // Images.  OpenCV's codecs are not available to C++ in this build: binary PGM / PPM (P5 / P6,
 // maxval 255) and the raw container the parity harness uses ("ACMRAW1 rows cols channels\n" +
-// bytes, channels in stored = BGR order) are read; anything else fails with a message.
-inline bool ReadImage(const std::string &path, Map<uint8_t> &out, std::string *err = nullptr) {
+// bytes, channels in stored = BGR order) are read here; JPEG streams are decoded on the device by
+// nvJPEG through the library when the including program defines ACMMP_IO_WITH_JPEG (and links
+// libacmmp_b200): `color` selects cv::imread's IMREAD_COLOR (BGR) or IMREAD_GRAYSCALE (luma).
+inline bool ReadImage(const std::string &path, Map<uint8_t> &out, std::string *err = nullptr, bool color = true, int device = 0) {
     FILE *f = fopen(path.c_str(), "rb");
     if (!f) {
         if (err) *err = "cannot open " + path;
         return false;
     }
+    (void)color;
+    (void)device;
+#ifdef ACMMP_IO_WITH_JPEG
+    {
+        unsigned char soi[2] = {0, 0};
+        if (fread(soi, 1, 2, f) == 2 && soi[0] == 0xFF && soi[1] == 0xD8) {
+            fseek(f, 0, SEEK_END);
+            const long n = ftell(f);
+            fseek(f, 0, SEEK_SET);
+            std::vector<uint8_t> bytes((size_t)n);
+            const bool got = fread(bytes.data(), 1, bytes.size(), f) == bytes.size();
+            fclose(f);
+            int w = 0, h = 0;
+            if (!got || acmmp_decode_jpeg(device, bytes.data(), bytes.size(), color ? 1 : 0, nullptr, 0, &w, &h)) {
+                if (err) *err = path + ": " + (got ? acmmp_jpeg_last_error() : "read error");
+                return false;
+            }
+            out = Map<uint8_t>(h, w, color ? 3 : 1);
+            if (acmmp_decode_jpeg(device, bytes.data(), bytes.size(), color ? 1 : 0, out.data.data(), out.data.size(), &w, &h)) {
+                if (err) *err = path + ": " + acmmp_jpeg_last_error();
+                return false;
+            }
+            return true;
+        }
+        fseek(f, 0, SEEK_SET);
+    }
+#endif
     char magic[16] = {0};
     bool ok = false;
     if (fscanf(f, "%15s", magic) == 1) {

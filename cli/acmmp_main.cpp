@@ -14,6 +14,7 @@
 #include <string>
 #include <vector>
 
+#define ACMMP_IO_WITH_JPEG 1
 #include "../acmmp_b200/host/acmmp.hpp"
 
 using namespace acmmp_b200;
@@ -24,10 +25,10 @@ static std::string id_name(int id, const char *suffix) {
     return buf;
 }
 
-static bool find_image(const std::string &folder, int id, Map<uint8_t> &im, std::string &err) {
-    for (const char *ext : {".jpg", ".pgm", ".ppm", ".raw"}) {   // the tests keep the reference's .jpg name for the raw container
+static bool find_image(const std::string &folder, int id, Map<uint8_t> &im, std::string &err, bool color, int device) {
+    for (const char *ext : {".jpg", ".pgm", ".ppm", ".raw"}) {   // the parity tests keep the reference's .jpg name for the raw container
         std::string e;
-        if (ReadImage(folder + "/" + id_name(id, ext), im, &e)) return true;
+        if (ReadImage(folder + "/" + id_name(id, ext), im, &e, color, device)) return true;
         if (!e.empty() && e.find("cannot open") == std::string::npos) err = e;
     }
     if (err.empty()) err = "no image for id " + std::to_string(id) + " under " + folder;
@@ -95,7 +96,8 @@ int main(int argc, char **argv) {
                 return EXIT_FAILURE;
             }
             std::string err;
-            if (!find_image(dense_folder + "/images", id, images[i], err)) {
+            // grey read for PatchMatch (ACMMP.cpp:534-541); a JPEG is decoded straight to luma like imread(IMREAD_GRAYSCALE)
+            if (!find_image(dense_folder + "/images", id, images[i], err, false, device)) {
                 fprintf(stderr, "%s\n", err.c_str());
                 return EXIT_FAILURE;
             }
@@ -152,10 +154,10 @@ int main(int argc, char **argv) {
         if (fuse) {
             Fusion fusion(cams_out, pairs, device);
             for (int i = 0; i < n; ++i) {
-                Map<uint8_t> color = images[i];
-                if (image_dir != "/images") {
+                Map<uint8_t> color;   // colour read for the point colours (acmmp_definitions.cpp:857)
+                {
                     std::string err;
-                    if (!find_image(dense_folder + image_dir, problems[i].ref_image_id, color, err)) {
+                    if (!find_image(dense_folder + image_dir, problems[i].ref_image_id, color, err, true, device)) {
                         fprintf(stderr, "%s\n", err.c_str());
                         return EXIT_FAILURE;
                     }
@@ -173,7 +175,7 @@ int main(int argc, char **argv) {
                 if (mask_dir != " ") {   // acmmp_definitions.cpp:870-895: mask = png < 128
                     Map<uint8_t> m;
                     std::string err;
-                    if (!find_image(dense_folder + "/" + mask_dir, problems[i].ref_image_id, m, err) || m.cols != cams_out[i].width || m.rows != cams_out[i].height) {
+                    if (!find_image(dense_folder + "/" + mask_dir, problems[i].ref_image_id, m, err, false, device) || m.cols != cams_out[i].width || m.rows != cams_out[i].height) {
                         fprintf(stderr, "mask of image %d missing or of the wrong size\n", problems[i].ref_image_id);
                         return EXIT_FAILURE;
                     }

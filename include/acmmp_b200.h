@@ -20,6 +20,7 @@
 #ifndef ACMMP_B200_H_
 #define ACMMP_B200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -349,6 +350,16 @@ int acmmp_fusion_get_points(acmmp_fusion *f, float *points9, int64_t capacity, i
 int acmmp_fusion_get_mask(acmmp_fusion *f, int view, uint8_t *mask);
 /* device ms of the last run: {score, greedy fixed point, compaction}; fixed-point rounds per view */
 int acmmp_fusion_stats(acmmp_fusion *f, double ms[3], int32_t *rounds_per_view);
+
+/* ==== JPEG decode on the device (nvJPEG) ======================================
+ * What the reference gets from cv::imread: mode 0 = IMREAD_GRAYSCALE (the luma
+ * plane, ACMMP.cpp:534-541), mode 1 = IMREAD_COLOR (interleaved BGR,
+ * acmmp_definitions.cpp:857).  `out` is a HOST buffer of width*height*(1|3)
+ * bytes; with out == NULL only the size is returned. */
+int acmmp_jpeg_info(const uint8_t *jpeg, size_t nbytes, int *width, int *height, int *components);
+int acmmp_decode_jpeg(int device, const uint8_t *jpeg, size_t nbytes, int mode, uint8_t *out,
+                      size_t capacity, int *width, int *height);
+const char *acmmp_jpeg_last_error(void);
 
 #ifdef __cplusplus
 }

@@ -104,3 +104,30 @@ def test_reference_runfusion_reads_the_cli_output(cli_run):
         same = (ref_xyz_n.view(np.uint32) == xyz_n.view(np.uint32)).all(1).mean()
         assert same >= 0.999, same
         assert (ref_col == col).all()
+
+
+def test_cli_reads_real_jpegs(tmp_path):
+    """images/%08d.jpg as real JPEG files (decoded by nvJPEG inside the library)"""
+    cv2 = pytest.importorskip("cv2")
+    if not os.path.exists(EXE):
+        pytest.skip("build/acmmp_main not built (make cli)")
+    sc = make_scene(5, 320, 240, 4, seed=6)
+    dense = str(tmp_path / "dense")
+    os.makedirs(os.path.join(dense, "images"))
+    os.makedirs(os.path.join(dense, "cams"))
+    n = 5
+    with open(os.path.join(dense, "pair.txt"), "w") as f:
+        f.write("%d\n" % n)
+        for i in range(n):
+            f.write("%d\n%d " % (i, len(sc["pairs"][i])) + " ".join("%d 1.0" % j for j in sc["pairs"][i]) + "\n")
+    for i in range(n):
+        img = np.clip(np.rint(sc["images"][i]), 0, 255).astype(np.uint8)
+        assert cv2.imwrite(os.path.join(dense, "images", "%08d.jpg" % i), cv2.cvtColor(img, cv2.COLOR_GRAY2BGR), [cv2.IMWRITE_JPEG_QUALITY, 98])
+        refbind._write_cam(os.path.join(dense, "cams", "%08d_cam.txt" % i), sc["cams"][i])
+    out = subprocess.run([EXE, dense, "--seed", "5", "--output_dir", "/OUT"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    depth = read_dmb(os.path.join(dense, "OUT", "2333_%08d" % 2, "depths_geom.dmb"))
+    gt = sc["depths"][2]
+    assert (np.abs(depth - gt)[8:-8, 8:-8] / gt[8:-8, 8:-8] < 0.01).mean() >= 0.9
+    xyz_n, col = read_ply(os.path.join(dense, "OUT", "ACMMP_model.ply"))
+    assert len(xyz_n) > 50000 and col.max() > 0
