@@ -44,11 +44,19 @@ oracle/liboracle.so: $(wildcard oracle/*.c) $(wildcard oracle/*.h)
 
 # The reference's own kernels, compiled from where they lie (never copied into the
 # repo), sm_100 + the reference's flags; only built where /root/reference exists.
-ref: oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so
+ref: oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so
 oracle/_ref/libacmmp_ref.so: oracle/ref_harness.cu $(wildcard oracle/ref_stub/opencv2/*.hpp)
 	@if [ -d $(REF) ]; then mkdir -p oracle/_ref && \
 	$(NVCC) -O3 --use_fast_math --maxrregcount=128 -std=c++14 -gencode arch=compute_100,code=sm_100 \
 	  -Ioracle/ref_stub -I$(REF) -Iinclude -Xcompiler -fPIC -shared -o $@ oracle/ref_harness.cu -lcudart ; \
+	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
+
+# The reference PROGRAM (kernels + host class + ProcessProblem + JBU + RunFusion) in the order of its
+# main(); cv::Subdiv2D is served by the product's Delaunay (acmmp_b200/csrc/prior.cpp) through a hook.
+oracle/_ref/libacmmp_ref_full.so: oracle/ref_full_harness.cu acmmp_b200/csrc/prior.cpp $(wildcard oracle/ref_stub/opencv2/*.hpp)
+	@if [ -d $(REF) ]; then mkdir -p oracle/_ref && \
+	$(NVCC) -O3 --use_fast_math --maxrregcount=128 -std=c++14 -gencode arch=compute_100,code=sm_100 -w \
+	  -Ioracle/ref_stub -I$(REF) -Iinclude -Xcompiler -fPIC -shared -o $@ oracle/ref_full_harness.cu acmmp_b200/csrc/prior.cpp -lcudart ; \
 	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
 
 # The reference's HOST code (RunFusion + helpers: ACMMP.cpp, acmmp_definitions.cpp) against the
@@ -66,5 +74,5 @@ oracle/_ref/libacmmp_ref_host_ieee.so: $(REF_HOST_SRC)
 	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
 
 clean:
-	rm -f $(LIB) build/fusion.o oracle/liboracle.so oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so
+	rm -f $(LIB) build/fusion.o oracle/liboracle.so oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so
 .PHONY: all oracle ref cli clean

@@ -141,8 +141,12 @@ int fail(acmmp_ctx *ctx, int code, const char *fmt, ...) {
                         __FILE__, __LINE__);                                                   \
     } while (0)
 
+// Every entry point starts here.  cudaGetLastError() drops a non-sticky error that OTHER code in the
+// process may have left in this thread's runtime state (the launch wrappers read it right after
+// their launch and would otherwise report somebody else's failure); sticky errors survive.
 int bind_device(acmmp_ctx *ctx) {
     CU(ctx, cudaSetDevice(ctx->device));
+    (void)cudaGetLastError();
     return 0;
 }
 

@@ -517,6 +517,7 @@ int acmmp_fusion_set_view(acmmp_fusion *f, int view, const float *depth, const f
     if (!f || !depth || !normal3) return ACMMP_ERR_INVALID;
     if (view < 0 || view >= f->n) return ffail(f, ACMMP_ERR_INVALID, "view %d out of range", view);
     FCU(f, cudaSetDevice(f->device));
+    (void)cudaGetLastError();   // drop a stale non-sticky error left by other code in the process
     const size_t P = (size_t)f->cams[view].width * f->cams[view].height;
     FusionView &v = f->views[view];
     const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
@@ -546,6 +547,7 @@ int acmmp_fusion_set_view(acmmp_fusion *f, int view, const float *depth, const f
 int acmmp_fusion_run(acmmp_fusion *f, float consistency_scalar, int con_num_thresh, int64_t *num_points) {
     if (!f) return ACMMP_ERR_INVALID;
     FCU(f, cudaSetDevice(f->device));
+    (void)cudaGetLastError();   // drop a stale non-sticky error left by other code in the process
     size_t maxP = 0;
     int max_src = 1;
     for (int v = 0; v < f->n; ++v) {
@@ -689,6 +691,7 @@ int acmmp_fusion_run(acmmp_fusion *f, float consistency_scalar, int con_num_thre
 int acmmp_fusion_get_points(acmmp_fusion *f, float *points9, int64_t capacity, int64_t *per_view_counts) {
     if (!f) return ACMMP_ERR_INVALID;
     FCU(f, cudaSetDevice(f->device));
+    (void)cudaGetLastError();   // drop a stale non-sticky error left by other code in the process
     if (points9) {
         if (capacity < (int64_t)f->points_n) return ffail(f, ACMMP_ERR_INVALID, "capacity %lld < %zu points", (long long)capacity, f->points_n);
         if (f->points_n) FCU(f, cudaMemcpyAsync(points9, f->points, f->points_n * 9 * sizeof(float), cudaMemcpyDeviceToHost, f->stream));
@@ -702,6 +705,7 @@ int acmmp_fusion_get_points(acmmp_fusion *f, float *points9, int64_t capacity, i
 int acmmp_fusion_get_mask(acmmp_fusion *f, int view, uint8_t *mask) {
     if (!f || !mask || view < 0 || view >= f->n || !f->views[view].set) return ACMMP_ERR_INVALID;
     FCU(f, cudaSetDevice(f->device));
+    (void)cudaGetLastError();   // drop a stale non-sticky error left by other code in the process
     const size_t P = (size_t)f->cams[view].width * f->cams[view].height;
     FCU(f, cudaMemcpyAsync(mask, f->views[view].mask, P, cudaMemcpyDeviceToHost, f->stream));
     FCU(f, cudaStreamSynchronize(f->stream));

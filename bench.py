@@ -323,7 +323,74 @@ def cpu_baseline(args, sc, hyp_per_view):
 
 
 def run_reference(args):
-    """Baseline arm: the reference's own CUDA kernels (oracle/_ref, compiled from
+    """Baseline arm.  Preferred: the reference PROGRAM itself (oracle/_ref/libacmmp_ref_full.so: its
+    kernels, host class, ProcessProblem, JointBilateralUpsampling and RunFusion compiled from where
+    they lie, run in the order of its main() on its own on-disk layout, .dmb round trips included).
+    Each step = the whole schedule over a bounded sub-scan: the centre view of the rig and its
+    sources (nsrc + 1 views, every view paired with all the others), i.e. the per-view work of the
+    full scan.  1 GPU: the reference has no multi-GPU mode and no CPU PatchMatch."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refbind
+    if not refbind.full_available():
+        return run_reference_kernels(args)
+    import shutil
+    import tempfile
+    import torch
+    torch.cuda.set_device(0)
+    sc = make_scan_inputs(args, torch.device("cuda", 0))
+    n = args.views
+    centre = n // 2
+    sample = sorted(set([centre] + sc["pairs"][centre][:args.nsrc]))
+    images = [sc["images"][i].cpu().numpy() for i in sample]
+    cams = [sc["cams"][i] for i in sample]
+    pairs = [[j for j in range(len(sample)) if j != i] for i in range(len(sample))]
+    H, W = args.height, args.width
+    sizes = [(W // 2, H // 2), (W, H)] if max(W, H) > 1000 else [(W, H)]
+    hpv = hyp_evals_per_view(sizes)
+    dense = tempfile.mkdtemp(prefix="acmmp_ref_")
+    try:
+        refbind.write_dense_folder(dense, cams, images, pairs)
+        for _ in range(min(args.warmup, 1)):     # a synchronous, allocation-per-view flow: one warm-up pass is enough
+            refbind.full_run(dense, seed=1234, fuse=False)
+        t_pm = 0.0
+        t_fu = 0.0
+        with ClockSampler(0) as clocks:
+            for k in range(args.steps):
+                a, b = refbind.full_run(dense, seed=1234 + k, fuse=(k == args.steps - 1))
+                t_pm += a
+                t_fu = b
+        npts = len(refbind.read_ply(os.path.join(dense, "ACMMP", "ACMMP_model.ply"))[0])
+    finally:
+        shutil.rmtree(dense, ignore_errors=True)
+    v = len(sample) * args.steps / t_pm
+    line = {
+        "impl": "reference",
+        "metric": "views/s, DTU-shape 1600x1200 49-view full ACMMP (multi-scale + planar prior + geometric consistency)",
+        "value": v, "unit": "views/s", "n_gpus": 1, "steps": args.steps, "warmup": min(args.warmup, 1),
+        "ms_per_step": t_pm / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"configs[2]: DTU-shape {W}x{H} x {n} views, {args.nsrc} sources, full ACMMP", "levels": [list(x) for x in sizes],
+                   "sample_views": sample, "hyp_evals_per_view": hpv,
+                   "what": "the reference program (ACMMP.cu / ACMMP.cpp / acmmp_definitions.cpp compiled from where they lie, sm_100, its own flags) "
+                           "in the order of its main(): per view and stage its own image read + resize, texture set-up, RunPatchMatch, host "
+                           "planar prior and .dmb round trips; stand-ins: raw images instead of JPEG decode, the product's Delaunay for "
+                           "cv::Subdiv2D, inert imshow / imwrite, fixed seed"},
+        "mpix_hyp_per_s": v * hpv / 1e6,
+        "fusion": {"points": npts, "ms": t_fu * 1e3, "what": "its own RunFusion (CPU, 1 thread) on the sub-scan"},
+        "cpu_baseline": {"value": v, "unit": "views/s", "cores": 1, "kind": "reference",
+                         "sample": f"{len(sample)}-view sub-scan per step (view {centre} and its {args.nsrc} sources, every view paired with all the "
+                                   "others), all scales and stages; 1 B200 for the reference's CUDA kernels, 1 host thread for its CPU steps"},
+        "e2e": {"value": v, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "clocks": clocks.summary(),
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_reference_kernels(args):
+    """Fallback baseline arm (libacmmp_ref_full.so absent): the reference's own CUDA kernels (oracle/_ref, compiled from
     /root/reference/src/ACMMP.cu for sm_100 with the reference's flags) in the
     reference's own per-view / per-stage flow (oracle/ref_pipeline.py), 1 GPU - the
     reference has no multi-GPU mode and no CPU PatchMatch.  Each step = a bounded
@@ -331,9 +398,6 @@ def run_reference(args):
     with all their sources; views outside the sample contribute ground-truth depth
     maps to the geometric-consistency stages, so the work per view is that of the
     full scan."""
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
     import torch
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import refbind

@@ -6,9 +6,8 @@
 //   * libacmmp_ref_host.so (oracle/ref_host_harness.cpp): the reference's host code
 //     (RunFusion and its helpers) - uses the functional subset below: Mat / Mat_ storage and
 //     element access, zeros, clone, convertTo, imread (a raw container, see imread below),
-//     resize (bilinear / nearest).  Display, drawing, imwrite, Subdiv2D and SVD are inert:
-//     the code paths that need them (debug windows, planar-prior construction) are not run
-//     through this library.
+//     resize (bilinear / nearest), SVD::solveZ for 3 x 4 systems, Subdiv2D through a hook.
+//     Display, drawing and imwrite are inert (debug windows / debug images only).
 // Test infrastructure - not part of the product.
 #pragma once
 #include <cfloat>
@@ -231,15 +230,47 @@ inline void line(Mat &, Point, Point, const Scalar &, int = 1) {}
 inline void merge(const std::vector<Mat> &, Mat &) {}
 inline void merge(const Mat *, size_t, Mat &) {}
 
-// inert: planar-prior construction is not run through this stub
+// Subdiv2D: the including harness may provide a Delaunay triangulation through this hook
+// (oracle/ref_full_harness.cu passes the product's integer Delaunay, acmmp_b200/csrc/prior.cpp);
+// without a hook the triangle list is empty.  Unlike OpenCV there are no virtual outer vertices,
+// i.e. exactly the triangles that survive the reference's imageRC.contains() filter.
+}  // namespace cv
+extern "C" int (*acmmp_ref_stub_delaunay_hook)(const int *xy, int n, int *tris6, int capacity);
+namespace cv {
 struct Subdiv2D {
+    std::vector<int> pts;
     Subdiv2D() {}
     explicit Subdiv2D(Rect) {}
-    int insert(Point2f) { return 0; }
-    void getTriangleList(std::vector<Vec6f> &out) const { out.clear(); }
+    int insert(Point2f p) { pts.push_back((int)p.x); pts.push_back((int)p.y); return (int)pts.size() / 2 - 1; }
+    void getTriangleList(std::vector<Vec6f> &out) const {
+        out.clear();
+        if (!acmmp_ref_stub_delaunay_hook || pts.size() < 6) return;
+        std::vector<int> tris(pts.size() * 6 + 6);   // < 2n triangles, 6 ints each
+        const int nt = acmmp_ref_stub_delaunay_hook(pts.data(), (int)pts.size() / 2, tris.data(), (int)tris.size() / 6);
+        for (int t = 0; t < nt; ++t) {
+            Vec6f v;
+            for (int k = 0; k < 6; ++k) v[k] = (float)tris[6 * t + k];
+            out.push_back(v);
+        }
+    }
 };
+// solveZ for the one shape the reference uses (3 x 4, ACMMP.cpp:922-944): the unit null vector of
+// [X 1] = generalised cross product of the three rows (the sign is normalised by the caller)
 struct SVD {
-    static void solveZ(const Mat &, Mat &) {}
+    static void solveZ(const Mat &A, Mat &B) {
+        double a[3][4];
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 4; ++c) a[r][c] = A.at<float>(r, c);
+        auto det3 = [&](int c0, int c1, int c2) {
+            return a[0][c0] * (a[1][c1] * a[2][c2] - a[1][c2] * a[2][c1]) - a[0][c1] * (a[1][c0] * a[2][c2] - a[1][c2] * a[2][c0]) +
+                   a[0][c2] * (a[1][c0] * a[2][c1] - a[1][c1] * a[2][c0]);
+        };
+        double n[4] = {det3(1, 2, 3), -det3(0, 2, 3), det3(0, 1, 3), -det3(0, 1, 2)};
+        double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2] + n[3] * n[3]);
+        if (len == 0) len = 1;
+        if (B.empty()) B.create(4, 1, CV_32FC1);
+        for (int k = 0; k < 4; ++k) B.at<float>(k, 0) = (float)(n[k] / len);
+    }
 };
 
 }  // namespace cv

@@ -246,3 +246,71 @@ def host_fusion(workdir, cams, depths, normals, colors, pairs, consistency_scala
     pts[:, :6] = rec["f"]
     pts[:, 6:] = rec["c"]
     return pts
+
+
+# ---- the reference PROGRAM (kernels + host class + ProcessProblem + JBU + RunFusion) -----------
+REF_FULL_PATH = os.path.join(_REF_DIR, "libacmmp_ref_full.so")
+_ref_full = None
+
+
+def full_available():
+    return os.path.exists(REF_FULL_PATH)
+
+
+def write_dense_folder(dense, cams, images, pairs):
+    """the reference's input layout: images/%08d.jpg (raw container, see oracle/ref_stub), cams/, pair.txt"""
+    os.makedirs(os.path.join(dense, "images"), exist_ok=True)
+    os.makedirs(os.path.join(dense, "cams"), exist_ok=True)
+    n = len(cams)
+    with open(os.path.join(dense, "pair.txt"), "w") as f:
+        f.write("%d\n" % n)
+        for i in range(n):
+            f.write("%d\n%d " % (i, len(pairs[i])) + " ".join("%d 1.0" % j for j in pairs[i]) + "\n")
+    for i in range(n):
+        img = np.clip(np.rint(np.asarray(images[i])), 0, 255).astype(np.uint8)
+        with open(os.path.join(dense, "images", "%08d.jpg" % i), "wb") as f:
+            f.write(b"ACMRAW1 %d %d 1\n" % img.shape + img.tobytes())
+        _write_cam(os.path.join(dense, "cams", "%08d_cam.txt" % i), cams[i])
+
+
+def read_dmb(path):
+    hdr = np.fromfile(path, np.int32, 4)
+    a = np.fromfile(path, np.float32, offset=16)
+    return a.reshape(hdr[1], hdr[2]) if hdr[3] == 1 else a.reshape(hdr[1], hdr[2], hdr[3])
+
+
+def read_ply(path):
+    with open(path, "rb") as f:
+        blob = f.read()
+    end = blob.index(b"end_header\n") + len(b"end_header\n")
+    count = int([l for l in blob[:end].decode().splitlines() if l.startswith("element vertex")][0].split()[-1])
+    rec = np.frombuffer(blob[end:end + 27 * count], dtype=np.dtype([("f", "<f4", 6), ("c", "u1", 3)]))
+    return rec["f"].copy(), rec["c"].copy()
+
+
+def full_run(dense, seed=1234, fuse=True, consistency_scalar=0.3, num_consistent_thresh=1, output_dir="/ACMMP", quiet=True):
+    """The reference program on `dense` (written by write_dense_folder).  Returns seconds spent in
+    the PatchMatch schedule (all ProcessProblem + JBU calls, file round trips included) and in RunFusion."""
+    global _ref_full
+    if _ref_full is None:
+        _ref_full = C.CDLL(REF_FULL_PATH)
+        _ref_full.ref_full_run.argtypes = [C.c_char_p, C.c_char_p, C.c_uint64, C.c_int, C.c_float, C.c_int,
+                                           C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    a, b = C.c_double(), C.c_double()
+    saved = None
+    if quiet:   # the reference prints a few lines per view
+        import sys
+        sys.stdout.flush()
+        saved = os.dup(1)
+        devnull = os.open(os.devnull, os.O_WRONLY)
+        os.dup2(devnull, 1)
+        os.close(devnull)
+    try:
+        rc = _ref_full.ref_full_run(dense.encode(), output_dir.encode(), seed, int(fuse), consistency_scalar, num_consistent_thresh,
+                                    C.byref(a), C.byref(b))
+    finally:
+        if saved is not None:
+            os.dup2(saved, 1)
+            os.close(saved)
+    assert rc == 0
+    return a.value, b.value
