@@ -12,6 +12,9 @@
 #include "ACMMP.cpp"
 #include "acmmp_definitions.cpp"
 
+// no Delaunay behind cv::Subdiv2D in this library: the planar-prior path is not run through it
+extern "C" int (*acmmp_ref_stub_delaunay_hook)(const int *, int, int *, int) = nullptr;
+
 // members defined in the reference's ACMMP.cu (device side; not part of this library, never called)
 void ACMMP::RunPatchMatch() {}
 void JBU::CudaRun() {}
