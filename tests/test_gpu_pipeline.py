@@ -268,3 +268,46 @@ def test_full_size_properties_dtu_shape():
     gt = sc["depths"][5]
     assert (np.abs(d1 - gt) / gt < 0.01)[16:-16, 16:-16].mean() >= 0.95
     m.close()
+
+
+def test_ragged_and_edge_inputs():
+    """odd image sizes (no multiple of any tile), views of different sizes in one scan, a view with a
+    single source, and argument errors: the schedule runs, stays deterministic and sane."""
+    import cv2
+    sc = make_scene(5, 331, 247, 3, seed=9)
+    cams = [c.copy() for c in sc["cams"]]
+    images = [np.ascontiguousarray(im, np.float32) for im in sc["images"]]
+    depths = list(sc["depths"])
+    # view 4 at another resolution (ragged scan): resample the image, rescale the intrinsics
+    w2, h2 = 298, 221
+    sx, sy = w2 / 331.0, h2 / 247.0
+    images[4] = cv2.resize(images[4], (w2, h2), interpolation=cv2.INTER_LINEAR)
+    depths[4] = cv2.resize(depths[4], (w2, h2), interpolation=cv2.INTER_NEAREST)
+    cams[4].K[0] *= sx; cams[4].K[2] *= sx; cams[4].K[4] *= sy; cams[4].K[5] *= sy
+    cams[4].width, cams[4].height = w2, h2
+    pairs = [list(p) for p in sc["pairs"]]
+    pairs[1] = pairs[1][:1]                                  # a single source view
+    ragged = dict(sc, cams=cams, images=images, depths=depths, pairs=pairs)
+    a = run_scan(ragged, world=1, seed=5)
+    b = run_scan(ragged, world=2, seed=5)
+    for v in range(5):
+        d, n, c = a[v]
+        assert d.shape == depths[v].shape and n.shape == depths[v].shape + (3,)
+        # geometric stages add 0.2 x (reprojection error clamped to 3) to the photometric cost in [0, 2]
+        # (pixels where no source view gets a vote end with weight_norm = 0 -> NaN cost, as in the reference)
+        ok = np.isfinite(c)
+        assert np.isfinite(d).all() and ok.mean() >= 0.95 and c[ok].min() >= 0 and c[ok].max() <= 2.6001, (ok.mean(), c[ok].min(), c[ok].max())
+        for k in range(3):
+            assert (gu.bits(a[v][k]) == gu.bits(b[v][k])).all(), (v, k)
+        if v != 1:
+            gt = depths[v]
+            assert (np.abs(d - gt)[8:-8, 8:-8] / gt[8:-8, 8:-8] < 0.01).mean() >= 0.85, v
+    # argument errors are reported, not executed
+    with pytest.raises(L.AcmmpError):
+        host.Scan(cams, [[] for _ in range(5)])              # a view without sources
+    with pytest.raises(L.AcmmpError):
+        host.Scan(cams, [[7]] * 5)                            # source id out of range
+    s = host.Scan(cams, pairs)
+    with pytest.raises(L.AcmmpError):
+        s.begin_level(0)                                      # images not set
+    s.close()
