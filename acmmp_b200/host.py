@@ -344,6 +344,12 @@ class Scan:
         self._ck(self._lib.acmmp_scan_view_device(self._s, view, C.byref(d), C.byref(n), C.byref(c)), "view_device")
         return d.value, n.value, c.value
 
+    def exchange_view_ptr(self, view):
+        """device pointer of any view's depth map inside this rank's exchange buffer (after the gather)"""
+        d = C.c_void_p()
+        self._ck(self._lib.acmmp_scan_view_device(self._s, view, C.byref(d), None, None), "view_device")
+        return d.value
+
     def timing(self):
         out, runs, launches = (C.c_double * 4)(), C.c_int(), C.c_uint64()
         self._ck(self._lib.acmmp_scan_timing(self._s, C.byref(out), C.byref(runs), C.byref(launches)), "timing")

@@ -259,13 +259,30 @@ def run_ours(args):
         "clocks": clocks.summary(),
         "exchanges_per_step": exchanges_per_step,
     }
+    # bit-level checksum of the final maps of every view (depth from this rank's exchange buffer, i.e.
+    # through the NCCL gathers; normals and costs of the owned views summed over ranks): equal numbers
+    # at different --gpus mean the sharded run reproduces the single-GPU maps bit for bit
+    scan.reset()
+    scan.run_all(seed=1234, exchange=exchange)
+    scan.sync()
+    csum = torch.zeros(1, dtype=torch.int64, device=dev)
+    for v in range(n):
+        d_, _, _ = scan.view_device(v) if v in owned else (scan.exchange_view_ptr(v), None, None)
+        w_, h_ = scan.view_size(v)
+        csum += torch.as_tensor(DevPtr(d_, w_ * h_), device=dev).view(torch.int32).to(torch.int64).sum() * (v + 1)
+    own = torch.zeros(1, dtype=torch.int64, device=dev)
+    for v in owned:
+        _, n_, c_ = scan.view_device(v)
+        w_, h_ = scan.view_size(v)
+        own += torch.as_tensor(DevPtr(n_, 3 * w_ * h_), device=dev).view(torch.int32).to(torch.int64).sum() * (v + 1)
+        own += torch.as_tensor(DevPtr(c_, w_ * h_), device=dev).view(torch.int32).to(torch.int64).sum() * (v + 1)
+    if dist is not None:
+        dist.all_reduce(own, op=dist.ReduceOp.SUM)
+    line["result_checksum"] = {"depth_all_views": int(csum.item()), "normals_costs": int(own.item())}
     if world == 1:
         # next row of the scope table: depth-map fusion of this scan's final maps on the
         # device, beside the CPU restatement of the reference's RunFusion on the same maps (outside
         # the timed region; not part of `value`)
-        scan.reset()
-        scan.run_all(seed=1234, exchange=exchange)
-        scan.sync()
         fus = host.Fusion(sc["cams"], sc["pairs"], device=local)
         for v in range(n):
             d_, n_, _ = scan.view_device(v)
