@@ -279,22 +279,39 @@ def run_ours(args):
     if dist is not None:
         dist.all_reduce(own, op=dist.ReduceOp.SUM)
     line["result_checksum"] = {"depth_all_views": int(csum.item()), "normals_costs": int(own.item())}
-    if world == 1:
-        # next row of the scope table: depth-map fusion of this scan's final maps on the
-        # device, beside the CPU restatement of the reference's RunFusion on the same maps (outside
-        # the timed region; not part of `value`)
+    # next row of the scope table: depth-map fusion of this scan's final maps on the
+    # device, beside the CPU restatement of the reference's RunFusion on the same maps (outside the
+    # timed region; not part of `value`).  Sharded runs: fusion is sequential over views, so the normals
+    # are sent to rank 0 (depths are there already, in the exchange buffer) and rank 0 fuses
+    # ("replicas only" for this step).
+    gathered = {}
+    if world > 1:
+        for v in range(n):
+            w_, h_ = scan.view_size(v)
+            if v % world == rank and rank != 0:
+                _, n_, _ = scan.view_device(v)
+                dist.send(torch.as_tensor(DevPtr(n_, 3 * w_ * h_), device=dev), dst=0)
+            elif rank == 0 and v % world != 0:
+                gathered[v] = torch.empty(3 * w_ * h_, dtype=torch.float32, device=dev)
+                dist.recv(gathered[v], src=v % world)
+        torch.cuda.synchronize()
+    if rank == 0:
         fus = host.Fusion(sc["cams"], sc["pairs"], device=local)
         for v in range(n):
-            d_, n_, _ = scan.view_device(v)
-            fus.set_view(v, d_, n_, on_device=True)
+            if v in gathered:
+                fus.set_view(v, scan.exchange_view_ptr(v), gathered[v].data_ptr(), on_device=True)
+            else:
+                d_, n_, _ = scan.view_device(v)
+                fus.set_view(v, d_, n_, on_device=True)
         fus.run(0.3, 1)
         t0 = time.time()
         npts = fus.run(0.3, 1)
         fwall = time.time() - t0
         fst = fus.stats()
         line["fusion"] = {"points": int(npts), "ms": fwall * 1e3, "device_ms": fst["score_ms"] + fst["greedy_ms"] + fst["emit_ms"],
-                          "fixed_point_rounds_max": max(fst["rounds"]), "consistency_scalar": 0.3, "num_consistent_thresh": 1}
-        if not args.no_cpu_baseline:
+                          "fixed_point_rounds_max": max(fst["rounds"]), "consistency_scalar": 0.3, "num_consistent_thresh": 1,
+                          "where": "rank 0" + (" after gathering the normals over NCCL" if world > 1 else "")}
+        if world == 1 and not args.no_cpu_baseline:
             import oraclebind as ob
             maps = [scan.get_view(v, want_cost=False) for v in range(n)]
             t0 = time.time()
