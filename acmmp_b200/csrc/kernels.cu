@@ -440,6 +440,18 @@ cudaError_t launch_tex_peak(cudaTextureObject_t tex, int w, int h, int layers, i
     return cudaGetLastError();
 }
 
+// one bilinear fetch per coordinate, through the same texture set-up as the problem's views
+__global__ void tex_sample_kernel(cudaTextureObject_t tex, const float *__restrict__ xs, const float *__restrict__ ys, int n,
+                                  float *__restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = tex2DLayered<float>(tex, xs[i], ys[i], 0);
+}
+cudaError_t launch_tex_sample(cudaTextureObject_t tex, const float *xs, const float *ys, int n, float *out, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    tex_sample_kernel<<<(n + 255) / 256, 256, 0, st>>>(tex, xs, ys, n, out);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_fp32_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st) {
     fp32_peak_kernel<<<blocks, threads, 0, st>>>(scratch, iters);
     return cudaGetLastError();

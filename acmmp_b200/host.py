@@ -218,6 +218,16 @@ def resize_linear(image, new_w, new_h, device=0):
     return out
 
 
+def tex_sample(image, xs, ys, device=0):
+    """Bilinear fetches of `image` at (xs, ys) through the views' texture set-up (ACMMP.cpp:646-663)."""
+    lib = L.load()
+    img, x, y = L.f32(image), L.f32(xs).ravel(), L.f32(ys).ravel()
+    out = np.empty(len(x), np.float32)
+    _check(None, lib.acmmp_tex_sample(device, L.fptr(img), img.shape[1], img.shape[0], L.fptr(x), L.fptr(y), len(x), L.fptr(out)),
+           "tex_sample")
+    return out
+
+
 def DelaunayTriangulation(points):
     """points (n,2) int -> triangles (m,3,2) int (ACMMP.cpp:896-918); host only."""
     lib = L.load()

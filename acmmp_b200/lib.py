@@ -57,7 +57,7 @@ EXPORTS = [
     "acmmp_run_sweep", "acmmp_run_tail", "acmmp_get_result", "acmmp_get_maps",
     "acmmp_get_depth_device", "acmmp_get_state", "acmmp_set_state", "acmmp_width", "acmmp_height",
     "acmmp_sync", "acmmp_launch_count", "acmmp_last_timing", "acmmp_jbu_depth", "acmmp_resize_linear",
-    "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_measure_tex_peak", "acmmp_get_planar_prior", "acmmp_delaunay", "acmmp_timing_collect",
+    "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_measure_tex_peak", "acmmp_tex_sample", "acmmp_get_planar_prior", "acmmp_delaunay", "acmmp_timing_collect",
     "acmmp_count_ncc", "acmmp_ncc_count", "acmmp_scan_count_ncc", "acmmp_scan_ncc_count",
     "acmmp_fusion_create", "acmmp_fusion_destroy", "acmmp_fusion_last_error", "acmmp_fusion_set_view", "acmmp_fusion_run",
     "acmmp_fusion_get_points", "acmmp_fusion_get_mask", "acmmp_fusion_stats",
@@ -127,6 +127,7 @@ def load():
     lib.acmmp_rng_init_states.argtypes = [C.c_int, C.c_uint64, C.c_int, C.c_int, up]
     lib.acmmp_measure_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.acmmp_measure_tex_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.acmmp_tex_sample.argtypes = [C.c_int, fp, C.c_int, C.c_int, fp, fp, C.c_int, fp]
     i32p = C.POINTER(C.c_int32)
     lib.acmmp_scan_create.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.POINTER(Camera), i32p, i32p]
     lib.acmmp_scan_destroy.argtypes = [vp]

@@ -245,6 +245,10 @@ int acmmp_measure_fp32_peak(int device, double *tflops, double *mufu_gops);
  * DTU-shape problem: warp-coherent coordinates, and the propagation kernel's
  * access shape (8 hypotheses around each of 4 pixels per warp). */
 int acmmp_measure_tex_peak(int device, double *coherent_gfetch, double *grouped_gfetch);
+/* n bilinear fetches at (xs[i], ys[i]) (unnormalised, texel centres at +0.5) from a host image
+ * through the texture set-up of the problem's views (reference: ACMMP.cpp:646-663).  Known-answer
+ * hook for the filter emulation of the test oracle (oracle/cost.c: orc_tex_bilinear). */
+int acmmp_tex_sample(int device, const float *image, int width, int height, const float *xs, const float *ys, int n, float *out);
 
 /* ==== whole-scan schedule ======================================================
  * The stage graph of main() (/root/reference/src/main_ACMMP.cpp:89-176) over a

@@ -175,3 +175,28 @@ def test_tail_and_resize_vs_cpu_oracle():
     rel = np.abs(after[..., 3] - orc.planes[..., 3])[ok] / np.maximum(np.abs(orc.planes[..., 3][ok]), 1e-6)
     assert (rel <= 1e-5).mean() >= 0.999
     m.close()
+
+
+def test_oracle_texture_filter_equals_hardware():
+    """The oracle's bilinear filter (oracle/cost.c: orc_tex_bilinear, 2-D weights in 1/256 units)
+    against the texture unit: bit-exact on 8-bit grey images (what the finest level of a scan
+    holds), >= 99.5 % bit-exact and within 2^-15 (texels in 0..255) on arbitrary fp32 texels (resized levels)."""
+    rng = np.random.default_rng(5)
+    w, h, n = 96, 64, 200000
+    xs = rng.uniform(-3.0, w + 3.0, n).astype(np.float32)
+    ys = rng.uniform(-3.0, h + 3.0, n).astype(np.float32)
+    # every (a, b) weight pair once, inside one texel cell
+    aa, bb = np.meshgrid(np.arange(256, dtype=np.float32), np.arange(256, dtype=np.float32))
+    xs[:65536] = 10.5 + aa.ravel() / 256.0
+    ys[:65536] = 20.5 + bb.ravel() / 256.0
+    img8 = rng.integers(0, 256, (h, w)).astype(np.float32)
+    hw = host.tex_sample(img8, xs, ys)
+    mine = np.array([ob.tex_bilinear(img8, float(x), float(y)) for x, y in zip(xs, ys)], np.float32)
+    assert (hw.view(np.uint32) == mine.view(np.uint32)).all()
+    imgf = (rng.random((h, w)) * 255.0).astype(np.float32)
+    hw = host.tex_sample(imgf, xs, ys)
+    mine = np.array([ob.tex_bilinear(imgf, float(x), float(y)) for x, y in zip(xs, ys)], np.float32)
+    same = hw.view(np.uint32) == mine.view(np.uint32)
+    assert same.mean() >= 0.995, same.mean()
+    # the rest: one unit in the last place of the largest texel (the filter's internal precision)
+    assert np.abs(hw - mine).max() <= 2.0 ** -15, np.abs(hw - mine).max()

@@ -2,12 +2,12 @@
 REFERENCE's own CUDA kernels on a B200 (tests/golden/ref_golden.npz).
 
 Tolerances: the reference build evaluates 1/x, sqrt, exp with MUFU approximations
-(--use_fast_math) and samples source images through the texture unit, whose
-bilinear weights have 8 fractional bits; the oracle uses exact libm and an
-emulation of that filter.  A sample whose source coordinate lands within ~1e-5 px
-of a 1/256 weight step takes the neighbouring weight on one side, which moves the
-cost by up to ~2e-3.  Hence: mean |d| <= 5e-5, >= 92 % of samples within 1e-4
-(north_star's NCC tolerance), max <= 1e-2.  The product CUDA path itself is held
+(--use_fast_math) and samples source images through the texture unit; the oracle uses
+exact libm and an emulation of that filter with the hardware's own 2-D weights (multiples
+of 1/256, rule measured on B200 - oracle/cost.c: orc_tex_bilinear).  A sample whose source
+coordinate lands within ~1e-5 px of a 1/256 weight step can still take the neighbouring
+weight, which moves the cost by up to ~2e-3.  Hence: mean |d| <= 1e-5, >= 99 % of samples
+within 1e-4 (north_star's NCC tolerance), max <= 5e-3.  The product CUDA path itself is held
 to bit-exactness against the same vectors in test_gpu_parity.py."""
 import numpy as np
 
@@ -46,9 +46,9 @@ def test_ncc_against_reference_kernel():
             mine = pr.ncc_map(g["planes_" + tag], v)
             ref = g["ncc_" + tag][v - 1]
             d = np.abs(mine - ref)
-            assert d.mean() <= 5e-5, (tag, v, d.mean())
-            assert (d <= 1e-4).mean() >= 0.92, (tag, v, (d <= 1e-4).mean())
-            assert d.max() <= 1e-2, (tag, v, d.max())
+            assert d.mean() <= 1e-5, (tag, v, d.mean())
+            assert (d <= 1e-4).mean() >= 0.99, (tag, v, (d <= 1e-4).mean())
+            assert d.max() <= 5e-3, (tag, v, d.max())
             # the out-of-image / flat-patch exits agree exactly
             assert ((mine == 2.0) == (ref == 2.0)).mean() >= 0.999
 
@@ -60,7 +60,7 @@ def test_initial_cost_and_view_masks_against_reference_kernel():
         pr.init(ob.INIT_SEEDED)
         ref_c, ref_s = g["seeded_cost_" + tag], g["seeded_sel_" + tag]
         d = np.abs(pr.costs - ref_c)
-        assert d.mean() <= 5e-5 and d.max() <= 1e-2
+        assert d.mean() <= 1e-5 and d.max() <= 5e-3
         # view-selection masks: equal wherever the k-th cost is not a near tie
         ncc = np.stack([g["ncc_" + tag][v] for v in range(pr.n - 1)], -1)
         srt = np.sort(ncc, -1)
