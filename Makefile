@@ -34,8 +34,12 @@ build/fusion.o: $(CSRC)/fusion.cu include/acmmp_b200.h
 	@mkdir -p build
 	$(NVCC) $(FUSIONFLAGS) -c -o $@ $(CSRC)/fusion.cu
 
-$(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o -lnvjpeg_static -lculibos -lcudart
+build/pairs.o: $(CSRC)/pairs.cu include/acmmp_b200.h
+	@mkdir -p build
+	$(NVCC) $(FUSIONFLAGS) -c -o $@ $(CSRC)/pairs.cu
+
+$(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o -lnvjpeg_static -lculibos -lcudart
 
 oracle: oracle/liboracle.so
 
@@ -74,5 +78,5 @@ oracle/_ref/libacmmp_ref_host_ieee.so: $(REF_HOST_SRC)
 	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
 
 clean:
-	rm -f $(LIB) build/fusion.o oracle/liboracle.so oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so
+	rm -f $(LIB) build/fusion.o build/pairs.o oracle/liboracle.so oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so
 .PHONY: all oracle ref cli clean

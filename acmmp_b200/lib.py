@@ -62,6 +62,7 @@ EXPORTS = [
     "acmmp_fusion_create", "acmmp_fusion_destroy", "acmmp_fusion_last_error", "acmmp_fusion_set_view", "acmmp_fusion_run",
     "acmmp_fusion_get_points", "acmmp_fusion_get_mask", "acmmp_fusion_stats",
     "acmmp_jpeg_info", "acmmp_decode_jpeg", "acmmp_jpeg_last_error",
+    "acmmp_pair_scores", "acmmp_pairs_last_error",
     "acmmp_scan_create", "acmmp_scan_destroy", "acmmp_scan_last_error", "acmmp_scan_set_image",
     "acmmp_scan_set_shard", "acmmp_scan_set_sequential_geom", "acmmp_scan_num_levels", "acmmp_scan_begin_level",
     "acmmp_scan_run_stage", "acmmp_scan_exchange", "acmmp_scan_view_size", "acmmp_scan_get_view", "acmmp_scan_view_device",
@@ -160,6 +161,10 @@ def load():
     lib.acmmp_jpeg_info.argtypes = [vp, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.acmmp_decode_jpeg.argtypes = [C.c_int, vp, C.c_size_t, C.c_int, vp, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.acmmp_jpeg_last_error.restype = C.c_char_p
+    dp = C.POINTER(C.c_double)
+    lib.acmmp_pair_scores.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.c_int64, dp, dp,
+                                      C.c_double, C.c_double, dp, dp]
+    lib.acmmp_pairs_last_error.restype = C.c_char_p
     lib.acmmp_scan_view_device.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     lib.acmmp_scan_count_ncc.argtypes = [vp, C.c_int]
     lib.acmmp_scan_ncc_count.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]

@@ -365,6 +365,21 @@ int acmmp_decode_jpeg(int device, const uint8_t *jpeg, size_t nbytes, int mode, 
                       size_t capacity, int *width, int *height);
 const char *acmmp_jpeg_last_error(void);
 
+/* ==== input converter: view-pair scores ========================================
+ * Replaces calc_score and the pair loop of the reference's converter
+ * (/root/reference/python_scripts/colmap2mvsnet_acm.py:280-302, :399-413).
+ * Image v owns the keypoints obs_points[obs_offsets[v] .. obs_offsets[v+1]): the index of the
+ * keypoint's 3-D point in xyz (n_points x 3 doubles) or -1 when it has none (point3D_ids with the
+ * sparse model's ids renumbered 0..n_points-1).  centers: n_images x 3 camera centres (-R^T t).
+ * scores (n_images x n_images doubles, symmetric, zero diagonal): number of keypoints of image
+ * min(i, j) whose point is also seen by the other image, or 0 when the angle at rank
+ * int(quantile * n) of the sorted triangulation angles is below min_angle_deg (reference: 0.75, 1).
+ * device_ms (nullable): device time of sort + scoring, inputs resident. */
+int acmmp_pair_scores(int device, int n_images, const int64_t *obs_offsets, const int32_t *obs_points,
+                      int64_t n_points, const double *xyz, const double *centers, double min_angle_deg,
+                      double quantile, double *scores, double *device_ms);
+const char *acmmp_pairs_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif
