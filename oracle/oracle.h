@@ -102,6 +102,13 @@ long orc_fusion(int n, const orc_camera *cams, const float *const *depths, const
                 const uint8_t *const *colors, const int *pair_offsets, const int *pair_ids,
                 float consistency_scalar, int con_num_thresh, float *points, long capacity);
 
+/* prior-aware fusion (RunPriorAwareFusion, acmmp_definitions.cpp:443-826): two (depth, normal) sets per
+ * view; masks0 (nullable, per view nullable): 1 = ignore the pixel.  Same point layout as orc_fusion. */
+long orc_prior_fusion(int n, const orc_camera *cams, const float *const *depths, const float *const *normals,
+                      const float *const *depths2, const float *const *normals2, const uint8_t *const *colors,
+                      const uint8_t *const *masks0, const int *pair_offsets, const int *pair_ids, float consistency_scalar,
+                      int num_consistent_thresh, int single_match_penalty, float *points, long capacity);
+
 #ifdef __cplusplus
 }
 #endif

@@ -31,3 +31,20 @@ extern "C" int ref_host_run_fusion(const char *dense_folder, const char *out_fol
     RunFusion(dense, out, problems, geom_consistency != 0, consistency_scalar, con_num_thresh, std::string("/images"), std::string(" "));
     return 0;
 }
+
+// RunPriorAwareFusion (acmmp_definitions.cpp:575-826): map set 0 is read from `fusion_folder`, set 1
+// from `out_folder`; writes <out_folder>/ACMMP_prior_model.ply
+extern "C" int ref_host_run_prior_fusion(const char *dense_folder, const char *out_folder, const char *fusion_folder, int n_views,
+                                         const int *image_ids, const int *pair_offsets, const int *pair_image_ids,
+                                         int geom_consistency, float consistency_scalar, int num_consistent_thresh,
+                                         int single_match_penalty) {
+    std::vector<Problem> problems(n_views);
+    for (int i = 0; i < n_views; ++i) {
+        problems[i].ref_image_id = image_ids[i];
+        for (int k = pair_offsets[i]; k < pair_offsets[i + 1]; ++k) problems[i].src_image_ids.push_back(pair_image_ids[k]);
+    }
+    std::string dense(dense_folder), out(out_folder), fus(fusion_folder);
+    RunPriorAwareFusion(dense, out, fus, problems, geom_consistency != 0, consistency_scalar, num_consistent_thresh,
+                        single_match_penalty, std::string(" "));
+    return 0;
+}

@@ -203,3 +203,127 @@ long orc_fusion(int n, const orc_camera *cams, const float *const *depths, const
     free(masks);
     return count;
 }
+
+/* ---- RunPriorAwareFusion, acmmp_definitions.cpp:443-826 ------------------------------------------
+ * Two (depth, normal) maps per view: set 0 from the fusion folder, set 1 from the run's own output
+ * folder (:607-643).  A pixel tries both of its hypotheses against both maps of every source view;
+ * the hypothesis with more consistent sources wins, a hypothesis that passes alone needs
+ * single_match_penalty more consistent sources (:746-776).  Only the winner's consistent source
+ * pixels are masked (:816-820) - there is no stale used_list here.
+ * Pinned against the reference's own function through oracle/ref_host_harness.cpp
+ * (tests/test_fusion_pinned.py). */
+typedef struct {
+    int below;     /* any of the two source maps passes the three thresholds (:487-516) */
+    float dyn;
+    size_t sidx;
+} paf_cand;
+
+static void paf_metric(const orc_camera *ref, const orc_camera *src, int r, int c, float ref_depth, const float *ref_normal,
+                       int src_r, int src_c, float src_depth, const float *src_normal, int *ok, float *dc) {
+    float reproj = 1e6f, rel = 1e6f, ang = 1e6f;                      /* cmetric defaults (:450-452) */
+    if (src_depth > 0) {
+        float T[3], tx, ty, pd;
+        world_point(src, src_c, src_r, src_depth, T);
+        project(ref, T, &tx, &ty, &pd);
+        reproj = (float)sqrt(pow(c - tx, 2) + pow(r - ty, 2));
+        rel = fabsf(pd - ref_depth) / ref_depth;
+        ang = get_angle(ref_normal, src_normal);
+    }
+    *ok = reproj < 2.0f && rel < 0.01f && ang < 0.174533f;
+    *dc = (float)exp(-(reproj + 200 * rel + ang * 10));
+}
+
+static int paf_candidates(int n_unused, const orc_camera *cams, const float *const *depths, const float *const *normals,
+                          const float *const *depths2, const float *const *normals2, uint8_t *const *masks, const int *ngb,
+                          int num_ngb, int i, int r, int c, float ref_depth, const float *ref_normal, paf_cand *out) {
+    (void)n_unused;
+    int m = 0;
+    float X[3];
+    for (int j = 0; j < num_ngb; ++j) {                               /* getCandidates (:519-573) */
+        const int s = ngb[j];
+        float qx, qy, pd;
+        world_point(&cams[i], c, r, ref_depth, X);
+        project(&cams[s], X, &qx, &qy, &pd);
+        const int src_r = (int)(qy + 0.5f), src_c = (int)(qx + 0.5f);
+        if (!(src_c >= 0 && src_c < cams[s].width && src_r >= 0 && src_r < cams[s].height)) continue;
+        const size_t sidx = (size_t)src_r * cams[s].width + src_c;
+        if (masks[s][sidx] == 1) continue;
+        int ok0, ok1;
+        float dc0, dc1;
+        paf_metric(&cams[i], &cams[s], r, c, ref_depth, ref_normal, src_r, src_c, depths[s][sidx], normals[s] + 3 * sidx, &ok0, &dc0);
+        paf_metric(&cams[i], &cams[s], r, c, ref_depth, ref_normal, src_r, src_c, depths2[s][sidx], normals2[s] + 3 * sidx, &ok1, &dc1);
+        paf_cand cd;
+        cd.below = ok0 || ok1;
+        cd.dyn = ok0 && ok1 ? (float)fmax(dc0, dc1) : (ok0 ? dc0 : (ok1 ? dc1 : 0.0f));
+        cd.sidx = sidx;
+        cd.below = cd.below ? 1 + s : 0;                              /* keeps the view index for the marking */
+        out[m++] = cd;
+    }
+    return m;
+}
+
+long orc_prior_fusion(int n, const orc_camera *cams, const float *const *depths, const float *const *normals,
+                      const float *const *depths2, const float *const *normals2, const uint8_t *const *colors,
+                      const uint8_t *const *masks0, const int *pair_offsets, const int *pair_ids, float consistency_scalar,
+                      int num_consistent_thresh, int single_match_penalty, float *points, long capacity) {
+    uint8_t **masks = (uint8_t **)malloc(sizeof(uint8_t *) * n);
+    for (int i = 0; i < n; ++i) {
+        const size_t P = (size_t)cams[i].width * cams[i].height;
+        masks[i] = (uint8_t *)calloc(P, 1);
+        if (masks0 && masks0[i]) memcpy(masks[i], masks0[i], P);
+    }
+    long count = 0;
+    for (int i = 0; i < n; ++i) {
+        const int cols = cams[i].width, rows = cams[i].height;
+        const int num_ngb = pair_offsets[i + 1] - pair_offsets[i];
+        const int *ngb = pair_ids + pair_offsets[i];
+        paf_cand *c0 = (paf_cand *)malloc(sizeof(paf_cand) * (num_ngb > 0 ? num_ngb : 1));
+        paf_cand *c1 = (paf_cand *)malloc(sizeof(paf_cand) * (num_ngb > 0 ? num_ngb : 1));
+        for (int r = 0; r < rows; ++r)
+            for (int c = 0; c < cols; ++c) {
+                const size_t idx = (size_t)r * cols + c;
+                if (masks[i][idx] == 1) continue;
+                const float d0 = depths[i][idx], d1 = depths2[i][idx];
+                const float *n0 = normals[i] + 3 * idx, *n1 = normals2[i] + 3 * idx;
+                if (d0 <= 0.0 && d1 <= 0.0) continue;
+                float cons0 = 0, cons1 = 0;
+                int k0 = 0, k1 = 0, m0 = 0, m1 = 0, t0 = 0, t1 = 0;
+                if (d0 > 0.0) {
+                    m0 = paf_candidates(n, cams, depths, normals, depths2, normals2, masks, ngb, num_ngb, i, r, c, d0, n0, c0);
+                    for (int k = 0; k < m0; ++k)
+                        if (c0[k].below) { k0++; cons0 += c0[k].dyn; }
+                    t0 = k0 >= num_consistent_thresh && cons0 > consistency_scalar * k0;
+                }
+                if (d1 > 0.0) {
+                    m1 = paf_candidates(n, cams, depths, normals, depths2, normals2, masks, ngb, num_ngb, i, r, c, d1, n1, c1);
+                    for (int k = 0; k < m1; ++k)
+                        if (c1[k].below) { k1++; cons1 += c1[k].dyn; }
+                    t1 = k1 >= num_consistent_thresh && cons1 > consistency_scalar * k1;
+                }
+                int passing, sel;                                      /* (:746-776) */
+                if (t0 && t1) { passing = 1; sel = k1 >= k0; }
+                else if (t1) { passing = k1 >= num_consistent_thresh + single_match_penalty; sel = 1; }
+                else { passing = t0 && k0 >= num_consistent_thresh + single_match_penalty; sel = 0; }
+                if (!passing) continue;
+                const float gd = sel ? d1 : d0;
+                const float *gn = sel ? n1 : n0;
+                if (points && count < capacity) {
+                    float *o = points + count * 9;
+                    world_point(&cams[i], c, r, gd, o);
+                    o[3] = gn[0]; o[4] = gn[1]; o[5] = gn[2];
+                    if (colors && colors[i]) { o[6] = colors[i][idx * 3]; o[7] = colors[i][idx * 3 + 1]; o[8] = colors[i][idx * 3 + 2]; }
+                    else { o[6] = o[7] = o[8] = 0; }
+                }
+                count++;
+                const paf_cand *it = sel ? c1 : c0;
+                const int m = sel ? m1 : m0;
+                for (int k = 0; k < m; ++k)
+                    if (it[k].below) masks[it[k].below - 1][it[k].sidx] = 1;
+            }
+        free(c0);
+        free(c1);
+    }
+    for (int i = 0; i < n; ++i) free(masks[i]);
+    free(masks);
+    return count;
+}

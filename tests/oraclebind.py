@@ -84,6 +84,10 @@ def load():
                                C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_int), C.POINTER(C.c_int),
                                C.c_float, C.c_int, fp, C.c_long]
     lib.orc_fusion.restype = C.c_long
+    u8pp = C.POINTER(C.POINTER(C.c_uint8))
+    lib.orc_prior_fusion.argtypes = [C.c_int, C.POINTER(OrcCamera), C.POINTER(fp), C.POINTER(fp), C.POINTER(fp), C.POINTER(fp),
+                                     u8pp, u8pp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_float, C.c_int, C.c_int, fp, C.c_long]
+    lib.orc_prior_fusion.restype = C.c_long
     i32p = C.POINTER(C.c_int32)
     lib.orc_support_points.argtypes = [fp, C.c_int, C.c_int, i32p]
     lib.orc_prior_from_triangles.argtypes = [C.POINTER(OrcCamera), fp, C.c_int, C.c_int, i32p, C.c_int, C.c_float, C.c_float, fp, fp, up]
@@ -282,6 +286,34 @@ def fusion(cams, depths, normals, pairs, consistency_scalar=0.3, con_num_thresh=
     cnt = load().orc_fusion(n, cam_arr, dp, npz, cp, offs.ctypes.data_as(C.POINTER(C.c_int)),
                             ids.ctypes.data_as(C.POINTER(C.c_int)), consistency_scalar, con_num_thresh, _fp(pts), cap)
     return (int(cnt), pts[:cnt]) if want_points else int(cnt)
+
+
+def prior_fusion(cams, depths, normals, depths2, normals2, pairs, consistency_scalar=0.3, num_consistent_thresh=1,
+                 single_match_penalty=1, colors=None, masks=None):
+    """RunPriorAwareFusion restatement -> (count, points (count, 9))."""
+    n = len(cams)
+    cam_arr = (OrcCamera * n)(*[to_orc_camera(c) for c in cams])
+    keep = [[_f32(x) for x in arrs] for arrs in (depths, normals, depths2, normals2)]
+    ptrs = [(fp * n)(*[_fp(x) for x in arrs]) for arrs in keep]
+    offs = np.zeros(n + 1, np.int32)
+    for i, p in enumerate(pairs):
+        offs[i + 1] = offs[i] + len(p)
+    ids = np.ascontiguousarray([j for p in pairs for j in p], np.int32)
+    u8p = C.POINTER(C.c_uint8)
+
+    def bytes_of(arrs):
+        if arrs is None:
+            return None, None
+        k = [np.ascontiguousarray(a, np.uint8) for a in arrs]
+        return k, (u8p * n)(*[a.ctypes.data_as(u8p) for a in k])
+    kc, cp = bytes_of(colors)
+    km, mp = bytes_of(masks)
+    cap = int(sum(x.size for x in keep[0]))
+    pts = np.zeros((cap, 9), np.float32)
+    cnt = load().orc_prior_fusion(n, cam_arr, ptrs[0], ptrs[1], ptrs[2], ptrs[3], cp, mp, offs.ctypes.data_as(C.POINTER(C.c_int)),
+                                  ids.ctypes.data_as(C.POINTER(C.c_int)), consistency_scalar, num_consistent_thresh,
+                                  single_match_penalty, _fp(pts), cap)
+    return int(cnt), pts[:cnt]
 
 
 def support_points(costs):

@@ -248,6 +248,59 @@ def host_fusion(workdir, cams, depths, normals, colors, pairs, consistency_scala
     return pts
 
 
+def _read_ply_points(path):
+    with open(path, "rb") as f:
+        blob = f.read()
+    end = blob.index(b"end_header\n") + len(b"end_header\n")
+    count = int([l for l in blob[:end].decode().splitlines() if l.startswith("element vertex")][0].split()[-1])
+    rec = np.frombuffer(blob[end:end + 27 * count], dtype=np.dtype([("f", "<f4", 6), ("c", "u1", 3)]))
+    pts = np.zeros((count, 9), np.float32)
+    pts[:, :6] = rec["f"]
+    pts[:, 6:] = rec["c"]
+    return pts
+
+
+def host_prior_fusion(workdir, cams, depths, normals, depths2, normals2, colors, pairs, consistency_scalar=0.3,
+                      num_consistent_thresh=1, single_match_penalty=1, geom=True, build="ieee"):
+    """The reference's own RunPriorAwareFusion (acmmp_definitions.cpp:575-826) on its own on-disk layout:
+    map set 0 under <dense>/FUSION (its `fusion_folder`), set 1 under <dense>/ACMMP (its `outfolder`);
+    returns the points of ACMMP_prior_model.ply as (N, 9) floats."""
+    key = "prior_" + build
+    if key not in _ref_host:
+        lib = C.CDLL(REF_HOST_PATHS[build])
+        lib.ref_host_run_prior_fusion.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                                  C.POINTER(C.c_int), C.c_int, C.c_float, C.c_int, C.c_int]
+        _ref_host[key] = lib
+    n = len(cams)
+    dense = os.path.join(workdir, "dense")
+    out = os.path.join(dense, "ACMMP")
+    fus = os.path.join(dense, "FUSION")
+    os.makedirs(os.path.join(dense, "images"), exist_ok=True)
+    os.makedirs(os.path.join(dense, "cams"), exist_ok=True)
+    for i in range(n):
+        h, w = depths[i].shape
+        col = np.zeros((h, w, 3), np.uint8) if colors is None else np.ascontiguousarray(colors[i], np.uint8)
+        with open(os.path.join(dense, "images", "%08d.jpg" % i), "wb") as f:      # raw container, see oracle/ref_stub
+            f.write(b"ACMRAW1 %d %d 3\n" % (h, w))
+            f.write(col.tobytes())
+        _write_cam(os.path.join(dense, "cams", "%08d_cam.txt" % i), cams[i])
+        for folder, d, nm in ((fus, depths[i], normals[i]), (out, depths2[i], normals2[i])):
+            vd = os.path.join(folder, "2333_%08d" % i)
+            os.makedirs(vd, exist_ok=True)
+            _write_dmb(os.path.join(vd, "depths_geom.dmb" if geom else "depths.dmb"), d)
+            _write_dmb(os.path.join(vd, "normals.dmb"), nm)
+    ids = (C.c_int * n)(*range(n))
+    offs, flat = [0], []
+    for p in pairs:
+        flat += list(p)
+        offs.append(len(flat))
+    rc = _ref_host[key].ref_host_run_prior_fusion(dense.encode(), out.encode(), fus.encode(), n, ids, (C.c_int * (n + 1))(*offs),
+                                                  (C.c_int * max(1, len(flat)))(*flat), int(geom), float(consistency_scalar),
+                                                  int(num_consistent_thresh), int(single_match_penalty))
+    assert rc == 0
+    return _read_ply_points(os.path.join(out, "ACMMP_prior_model.ply"))
+
+
 # ---- the reference PROGRAM (kernels + host class + ProcessProblem + JBU + RunFusion) -----------
 REF_FULL_PATH = os.path.join(_REF_DIR, "libacmmp_ref_full.so")
 _ref_full = None

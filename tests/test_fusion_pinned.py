@@ -59,3 +59,42 @@ def test_used_list_quirk_is_exercised():
     # without stale coordinates every accepted pixel masks only its own consistent sources
     from fusion_inputs import fusion_no_stale
     assert fusion_no_stale(sc["cams"], depths, normals, sc["pairs"], 0.3, 2) != cnt
+
+
+# ---- prior-aware fusion ---------------------------------------------------
+
+def second_maps(sc, seed):
+    """the second (depth, normal) set of every view: another noisy run with its own holes"""
+    d2, n2, _ = noisy_maps(sc, seed, noise=0.003, holes=0.15, outliers=0.05)
+    return d2, n2
+
+
+@needs_ref_host
+@pytest.mark.parametrize("thresh,scalar,penalty", [(1, 0.3, 1), (2, 0.3, 1), (1, 0.1, 0), (2, 0.2, 2)])
+def test_prior_fusion_restatement_is_bit_exact_against_reference(thresh, scalar, penalty):
+    sc = make_scene(6, 160, 120, 4, seed=2)
+    depths, normals, colors = noisy_maps(sc, 11, holes=0.1)
+    depths2, normals2 = second_maps(sc, 12)
+    with tempfile.TemporaryDirectory() as d:
+        ref_pts = refbind.host_prior_fusion(d, sc["cams"], depths, normals, depths2, normals2, colors, sc["pairs"], scalar, thresh,
+                                            penalty, build="ieee")
+    cnt, pts = ob.prior_fusion(sc["cams"], depths, normals, depths2, normals2, sc["pairs"], scalar, thresh, penalty, colors=colors)
+    assert cnt > 1000 and len(ref_pts) == cnt
+    assert (ref_pts[:, :6].view(np.uint32) == pts[:, :6].view(np.uint32)).all()
+    assert (ref_pts[:, 6:] == pts[:, [8, 7, 6]]).all()
+    # both hypotheses win somewhere: points carry normals of set 0 and of set 1
+    key = lambda a: set(map(bytes, np.ascontiguousarray(a).view(np.uint8).reshape(len(a), -1)))  # noqa: E731
+    n0 = key(np.concatenate([x.reshape(-1, 3) for x in normals]))
+    n1 = key(np.concatenate([x.reshape(-1, 3) for x in normals2]))
+    got = key(pts[:, 3:6])
+    assert len(got & n0) > 100 and len(got & n1) > 100
+
+
+@needs_ref_host
+def test_prior_fusion_differs_from_plain_fusion():
+    sc = make_scene(5, 128, 96, 3, seed=4)
+    depths, normals, colors = noisy_maps(sc, 3, holes=0.1)
+    depths2, normals2 = second_maps(sc, 5)
+    cnt, _ = ob.prior_fusion(sc["cams"], depths, normals, depths2, normals2, sc["pairs"], 0.3, 1, 1, colors=colors)
+    plain = ob.fusion(sc["cams"], depths, normals, sc["pairs"], 0.3, 1)
+    assert cnt != plain and cnt > 0
