@@ -52,6 +52,9 @@ struct FusionView {
     float *depth = nullptr;      // P
     float *normal = nullptr;     // 3P
     uint8_t *color = nullptr;    // 3P or null
+    float *depth2 = nullptr;     // P: second map set (prior-aware fusion), else null
+    float *normal2 = nullptr;    // 3P
+    bool set2 = false;
     uint8_t *mask0 = nullptr;    // P: caller's mask (1 = ignore the pixel), kept so that a run can be repeated
     uint8_t *mask = nullptr;     // P: working mask: 1 = ignore / already used
     int *mark = nullptr;         // P: time (pixel index of the view being fused) at which the pixel gets masked
@@ -347,8 +350,9 @@ __global__ void fusion_offsets_kernel(const int *cnt, int nchunks, int *offs) {
 // points: 9 floats each = world point, normal of the reference pixel, colour bytes as stored
 // (acmmp_definitions.cpp:954-958,1013-1017)
 __global__ void __launch_bounds__(kScanThreads) fusion_emit_kernel(const __grid_constant__ FusionCam cam, const float *depth,
-                                                                   const float *normal, const uint8_t *color, const uint8_t *appr,
-                                                                   const int *offs, float *points) {
+                                                                   const float *normal, const float *depth2, const float *normal2,
+                                                                   const uint8_t *color, const uint8_t *appr, const int *offs,
+                                                                   float *points) {
     __shared__ int s_warp[kScanThreads / 32];
     const int P = cam.width * cam.height;
     const int base = blockIdx.x * kChunk + threadIdx.x * kPerThread;
@@ -376,11 +380,13 @@ __global__ void __launch_bounds__(kScanThreads) fusion_emit_kernel(const __grid_
         if ((ap >> k) & 1u) {
             const int p = base + k;
             const int r = p / cam.width, c = p - r * cam.width;
+            const bool second = appr[p] == 2;   // prior-aware fusion: the second hypothesis won
+            const float *nm = (second ? normal2 : normal) + 3 * (size_t)p;
             float X[3];
-            world_point(cam, c, r, depth[p], X);
+            world_point(cam, c, r, second ? depth2[p] : depth[p], X);
             float *o = points + (size_t)before * 9;
             o[0] = X[0]; o[1] = X[1]; o[2] = X[2];
-            o[3] = normal[3 * (size_t)p]; o[4] = normal[3 * (size_t)p + 1]; o[5] = normal[3 * (size_t)p + 2];
+            o[3] = nm[0]; o[4] = nm[1]; o[5] = nm[2];
             if (color) {
                 o[6] = (float)color[3 * (size_t)p]; o[7] = (float)color[3 * (size_t)p + 1]; o[8] = (float)color[3 * (size_t)p + 2];
             } else {
@@ -388,6 +394,139 @@ __global__ void __launch_bounds__(kScanThreads) fusion_emit_kernel(const __grid_
             }
             before++;
         }
+}
+
+// ---- prior-aware fusion (RunPriorAwareFusion, acmmp_definitions.cpp:443-826) ------------------
+// Two (depth, normal) sets per view.  A pixel tries both of its hypotheses (set 0, set 1) against
+// both maps of every source; per hypothesis h and source j the mask-independent part is
+//   loc[(h ns + j) P + p] = source pixel if either source map passes the three thresholds, else -1
+//   w  [(h ns + j) P + p] = its dynamic consistency (max over the passing source maps)   (:487-516)
+// The greedy pass is again a fixed point over mask times, simpler than RunFusion's: an accepted pixel
+// masks exactly the consistent source pixels of its winning hypothesis (:816-820), so
+// mark[x] = min over accepted pixels p that include x - one atomicMin scatter per round.
+struct PriorScoreArgs {
+    FusionCam ref;
+    FusionCam src[ACMMP_MAX_SRC_VIEWS];
+    const float *src_depth[2][ACMMP_MAX_SRC_VIEWS];
+    const float *src_normal[2][ACMMP_MAX_SRC_VIEWS];
+    int nsrc;
+};
+
+// get_consistency_metrics for one source map (:458-484, :498-503): passes = the three thresholds
+__device__ __forceinline__ void prior_metric(const FusionCam &ref, const FusionCam &s, int r, int c, float ref_depth, float n0,
+                                             float n1, float n2, int src_r, int src_c, float src_depth, const float *sn,
+                                             bool &passes, float &dc) {
+    float reproj = 1e6f, rel = 1e6f, ang = 1e6f;
+    if (src_depth > 0.0f) {
+        float T[3], tx, ty, pd;
+        world_point(s, src_c, src_r, src_depth, T);
+        project(ref, T, tx, ty, pd);
+        const double dx = (double)(c - tx), dy = (double)(r - ty);
+        reproj = (float)sqrt(dx * dx + dy * dy);
+        rel = fabsf(pd - ref_depth) / ref_depth;
+        const float dot = n0 * sn[0] + n1 * sn[1] + n2 * sn[2];
+        ang = acosf(dot);
+        if (ang != ang) ang = 0.0f;
+    }
+    passes = reproj < 2.0f && rel < 0.01f && ang < 0.174533f;
+    const float ti = reproj + 200 * rel + ang * 10;
+    dc = (float)exp((double)-ti);
+}
+
+__global__ void prior_score_kernel(const __grid_constant__ PriorScoreArgs a, const float *depth0, const float *normal0,
+                                   const float *depth1, const float *normal1, const uint8_t *mask, int *loc, float *w,
+                                   uint8_t *valid) {
+    const int P = a.ref.width * a.ref.height;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const int r = p / a.ref.width, c = p - r * a.ref.width;
+    const float d[2] = {depth0[p], depth1[p]};
+    const bool ok = mask[p] != 1 && !(d[0] <= 0.0f && d[1] <= 0.0f);     // (:686-697)
+    valid[p] = ok ? 1 : 0;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const float *nm = (h ? normal1 : normal0) + 3 * (size_t)p;
+        const float n0 = nm[0], n1 = nm[1], n2 = nm[2];
+        const bool live = ok && d[h] > 0.0f;
+        float X[3];
+        if (live) world_point(a.ref, c, r, d[h], X);
+        for (int j = 0; j < a.nsrc; ++j) {
+            int l = -1;
+            float wt = 0.0f;
+            if (live) {
+                const FusionCam &s = a.src[j];
+                float qx, qy, pd;
+                project(s, X, qx, qy, pd);
+                const int src_r = (int)(qy + 0.5f), src_c = (int)(qx + 0.5f);
+                if (src_c >= 0 && src_c < s.width && src_r >= 0 && src_r < s.height) {
+                    const int sidx = src_r * s.width + src_c;
+                    bool p0, p1;
+                    float dc0, dc1;
+                    prior_metric(a.ref, s, r, c, d[h], n0, n1, n2, src_r, src_c, a.src_depth[0][j][sidx],
+                                 a.src_normal[0][j] + 3 * (size_t)sidx, p0, dc0);
+                    prior_metric(a.ref, s, r, c, d[h], n0, n1, n2, src_r, src_c, a.src_depth[1][j][sidx],
+                                 a.src_normal[1][j] + 3 * (size_t)sidx, p1, dc1);
+                    if (p0 || p1) {
+                        l = sidx;
+                        wt = p0 && p1 ? fmaxf(dc0, dc1) : (p0 ? dc0 : dc1);
+                    }
+                }
+            }
+            loc[((size_t)h * a.nsrc + j) * P + p] = l;
+            w[((size_t)h * a.nsrc + j) * P + p] = wt;
+        }
+    }
+}
+
+// state of pixel p given the mask times: cons[h P + p] = sources consistent with hypothesis h and not
+// masked before p; appr = 0 rejected, 1 + h accepted with hypothesis h (:699-776)
+__global__ void prior_decide_kernel(const __grid_constant__ IterArgs a, int single_match_penalty, const int *loc, const float *w,
+                                    const uint8_t *valid, uint32_t *cons, uint8_t *appr, int *changed) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= a.P) return;
+    uint32_t bits[2] = {0u, 0u};
+    uint8_t ap = 0;
+    if (valid[p]) {
+        int num[2] = {0, 0};
+        bool thr[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            float dyn = 0.0f;
+            for (int j = 0; j < a.nsrc; ++j) {
+                const size_t at = ((size_t)h * a.nsrc + j) * a.P + p;
+                const int l = loc[at];
+                if (l >= 0 && !(a.mark[j][l] < p)) {
+                    bits[h] |= 1u << j;
+                    dyn += w[at];
+                    num[h]++;
+                }
+            }
+            thr[h] = num[h] >= a.con_num_thresh && dyn > a.consistency_scalar * num[h];
+        }
+        if (thr[0] && thr[1]) ap = num[1] >= num[0] ? 2 : 1;
+        else if (thr[1]) ap = num[1] >= a.con_num_thresh + single_match_penalty ? 2 : 0;
+        else ap = thr[0] && num[0] >= a.con_num_thresh + single_match_penalty ? 1 : 0;
+    }
+    if (bits[0] != cons[p] || bits[1] != cons[(size_t)a.P + p] || ap != appr[p]) {
+        cons[p] = bits[0];
+        cons[(size_t)a.P + p] = bits[1];
+        appr[p] = ap;
+        *changed = 1;
+    }
+}
+
+__global__ void prior_mark_kernel(const __grid_constant__ IterArgs a, const int *loc, const uint32_t *cons, const uint8_t *appr) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= a.P) return;
+    const int ap = appr[p];
+    if (!ap) return;
+    const int h = ap - 1;
+    uint32_t bits = cons[(size_t)h * a.P + p];
+    while (bits) {
+        const int j = __ffs(bits) - 1;
+        bits &= bits - 1;
+        atomicMin(a.mark[j] + loc[((size_t)h * a.nsrc + j) * a.P + p], p);
+    }
 }
 
 }  // namespace
@@ -405,6 +544,7 @@ struct acmmp_fusion {
     // per-view scratch, sized for the largest view
     size_t cap_pixels = 0;
     int max_src = 0;
+    int cap_hyps = 0;
     int *loc = nullptr;
     float *w = nullptr;
     uint8_t *valid = nullptr, *appr = nullptr;
@@ -502,6 +642,7 @@ void acmmp_fusion_destroy(acmmp_fusion *f) {
     if (f->stream) cudaStreamSynchronize(f->stream);
     for (auto &v : f->views) {
         cudaFree(v.depth); cudaFree(v.normal); cudaFree(v.color); cudaFree(v.mask0); cudaFree(v.mask); cudaFree(v.mark);
+        cudaFree(v.depth2); cudaFree(v.normal2);
     }
     free_scratch(f);
     cudaFree(f->changed);
@@ -544,34 +685,39 @@ int acmmp_fusion_set_view(acmmp_fusion *f, int view, const float *depth, const f
     return 0;
 }
 
-int acmmp_fusion_run(acmmp_fusion *f, float consistency_scalar, int con_num_thresh, int64_t *num_points) {
+// both fusions: per view score -> fixed-point greedy pass -> ordered compaction
+static int fusion_run_impl(acmmp_fusion *f, float consistency_scalar, int con_num_thresh, bool prior, int single_match_penalty,
+                           int64_t *num_points) {
     if (!f) return ACMMP_ERR_INVALID;
+    const int hyps = prior ? 2 : 1;
     FCU(f, cudaSetDevice(f->device));
     (void)cudaGetLastError();   // drop a stale non-sticky error left by other code in the process
     size_t maxP = 0;
     int max_src = 1;
     for (int v = 0; v < f->n; ++v) {
         if (!f->views[v].set) return ffail(f, ACMMP_ERR_STATE, "maps of view %d not set", v);
+        if (prior && !f->views[v].set2) return ffail(f, ACMMP_ERR_STATE, "second maps of view %d not set", v);
         const size_t P = (size_t)f->cams[v].width * f->cams[v].height;
         if (P > maxP) maxP = P;
         const int ns = f->pair_off[v + 1] - f->pair_off[v];
         if (ns > max_src) max_src = ns;
     }
     const int max_chunks = (int)((maxP + kChunk - 1) / kChunk);
-    if (maxP > f->cap_pixels || max_src > f->max_src) {
+    if (maxP > f->cap_pixels || max_src > f->max_src || hyps > f->cap_hyps) {
         FCU(f, cudaStreamSynchronize(f->stream));
         free_scratch(f);
-        FCU(f, dalloc(&f->loc, maxP * max_src));
-        FCU(f, dalloc(&f->w, maxP * max_src));
+        FCU(f, dalloc(&f->loc, maxP * max_src * hyps));
+        FCU(f, dalloc(&f->w, maxP * max_src * hyps));
         FCU(f, dalloc(&f->valid, maxP));
         FCU(f, dalloc(&f->appr, maxP));
-        FCU(f, dalloc(&f->cons, maxP));
+        FCU(f, dalloc(&f->cons, maxP * hyps));
         FCU(f, dalloc(&f->agg, (size_t)(max_src + 1) * max_chunks));
         FCU(f, dalloc(&f->carry, (size_t)(max_src + 1) * max_chunks));
         FCU(f, dalloc(&f->cnt, (size_t)max_chunks));
         FCU(f, dalloc(&f->offs, (size_t)max_chunks + 1));
         f->cap_pixels = maxP;
         f->max_src = max_src;
+        f->cap_hyps = hyps;
     }
     cudaStream_t st = f->stream;
     for (int v = 0; v < f->n; ++v) {
@@ -614,17 +760,35 @@ int acmmp_fusion_run(acmmp_fusion *f, float consistency_scalar, int con_num_thre
             return cudaGetLastError();
         };
         FCU(f, cudaEventRecord(ev[0], st));
-        fusion_score_kernel<<<pblocks, 256, 0, st>>>(sa, V.depth, V.normal, V.mask, f->loc, f->w, f->valid);
+        if (prior) {
+            PriorScoreArgs pa;
+            memset(&pa, 0, sizeof pa);
+            pa.ref = sa.ref;
+            pa.nsrc = ns;
+            for (int j = 0; j < ns; ++j) {
+                pa.src[j] = sa.src[j];
+                pa.src_depth[0][j] = f->views[ngb[j]].depth;
+                pa.src_normal[0][j] = f->views[ngb[j]].normal;
+                pa.src_depth[1][j] = f->views[ngb[j]].depth2;
+                pa.src_normal[1][j] = f->views[ngb[j]].normal2;
+            }
+            prior_score_kernel<<<pblocks, 256, 0, st>>>(pa, V.depth, V.normal, V.depth2, V.normal2, V.mask, f->loc, f->w, f->valid);
+        } else {
+            fusion_score_kernel<<<pblocks, 256, 0, st>>>(sa, V.depth, V.normal, V.mask, f->loc, f->w, f->valid);
+        }
         FCU(f, cudaGetLastError());
         FCU(f, cudaEventRecord(ev[1], st));
-        FCU(f, cudaMemsetAsync(f->cons, 0, (size_t)P * sizeof(uint32_t), st));
+        FCU(f, cudaMemsetAsync(f->cons, 0, (size_t)P * hyps * sizeof(uint32_t), st));
         FCU(f, cudaMemsetAsync(f->appr, 0, (size_t)P, st));
         FCU(f, reset_marks());
         int rounds = 0;
         for (;;) {
             int changed = 0;
             FCU(f, cudaMemsetAsync(f->changed, 0, sizeof(int), st));
-            fusion_decide_kernel<<<pblocks, 256, 0, st>>>(ia, f->loc, f->w, f->valid, f->cons, f->appr, f->changed);
+            if (prior)
+                prior_decide_kernel<<<pblocks, 256, 0, st>>>(ia, single_match_penalty, f->loc, f->w, f->valid, f->cons, f->appr, f->changed);
+            else
+                fusion_decide_kernel<<<pblocks, 256, 0, st>>>(ia, f->loc, f->w, f->valid, f->cons, f->appr, f->changed);
             FCU(f, cudaGetLastError());
             FCU(f, cudaMemcpyAsync(&changed, f->changed, sizeof(int), cudaMemcpyDeviceToHost, st));
             FCU(f, cudaStreamSynchronize(st));
@@ -635,9 +799,13 @@ int acmmp_fusion_run(acmmp_fusion *f, float consistency_scalar, int con_num_thre
                 break;
             }
             FCU(f, reset_marks());
-            fusion_chunk_min_kernel<<<nchunks, kScanThreads, 0, st>>>(f->cons, f->appr, P, ns + 1, nchunks, f->agg);
-            fusion_agg_scan_kernel<<<ns + 1, 32, 0, st>>>(f->agg, nchunks, f->carry);
-            fusion_mark_kernel<<<nchunks, kScanThreads, 0, st>>>(ia, f->cons, f->appr, f->loc, f->carry, nchunks);
+            if (prior) {
+                prior_mark_kernel<<<pblocks, 256, 0, st>>>(ia, f->loc, f->cons, f->appr);
+            } else {
+                fusion_chunk_min_kernel<<<nchunks, kScanThreads, 0, st>>>(f->cons, f->appr, P, ns + 1, nchunks, f->agg);
+                fusion_agg_scan_kernel<<<ns + 1, 32, 0, st>>>(f->agg, nchunks, f->carry);
+                fusion_mark_kernel<<<nchunks, kScanThreads, 0, st>>>(ia, f->cons, f->appr, f->loc, f->carry, nchunks);
+            }
             FCU(f, cudaGetLastError());
         }
         if (rc) break;
@@ -667,8 +835,9 @@ int acmmp_fusion_run(acmmp_fusion *f, float consistency_scalar, int con_num_thre
             f->points_cap = cap;
         }
         if (total > 0) {
-            fusion_emit_kernel<<<nchunks, kScanThreads, 0, st>>>(sa.ref, V.depth, V.normal, V.color, f->appr, f->offs,
-                                                                 f->points + f->points_n * 9);
+            fusion_emit_kernel<<<nchunks, kScanThreads, 0, st>>>(sa.ref, V.depth, V.normal, prior ? V.depth2 : nullptr,
+                                                                 prior ? V.normal2 : nullptr, V.color, f->appr,
+                                                                 f->offs, f->points + f->points_n * 9);
             FCU(f, cudaGetLastError());
         }
         f->points_n += (size_t)total;
@@ -685,6 +854,34 @@ int acmmp_fusion_run(acmmp_fusion *f, float consistency_scalar, int con_num_thre
     for (auto &e : ev) cudaEventDestroy(e);
     if (rc) return rc;
     if (num_points) *num_points = (int64_t)f->points_n;
+    return 0;
+}
+
+int acmmp_fusion_run(acmmp_fusion *f, float consistency_scalar, int con_num_thresh, int64_t *num_points) {
+    return fusion_run_impl(f, consistency_scalar, con_num_thresh, false, 0, num_points);
+}
+
+int acmmp_fusion_run_prior_aware(acmmp_fusion *f, float consistency_scalar, int num_consistent_thresh, int single_match_penalty,
+                                 int64_t *num_points) {
+    return fusion_run_impl(f, consistency_scalar, num_consistent_thresh, true, single_match_penalty, num_points);
+}
+
+int acmmp_fusion_set_view_second(acmmp_fusion *f, int view, const float *depth2, const float *normal3_2, int on_device) {
+    if (!f || !depth2 || !normal3_2) return ACMMP_ERR_INVALID;
+    if (view < 0 || view >= f->n) return ffail(f, ACMMP_ERR_INVALID, "view %d out of range", view);
+    FCU(f, cudaSetDevice(f->device));
+    (void)cudaGetLastError();   // drop a stale non-sticky error left by other code in the process
+    const size_t P = (size_t)f->cams[view].width * f->cams[view].height;
+    FusionView &v = f->views[view];
+    const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    if (!v.depth2) {
+        FCU(f, dalloc(&v.depth2, P));
+        FCU(f, dalloc(&v.normal2, 3 * P));
+    }
+    FCU(f, cudaMemcpyAsync(v.depth2, depth2, P * sizeof(float), kind, f->stream));
+    FCU(f, cudaMemcpyAsync(v.normal2, normal3_2, 3 * P * sizeof(float), kind, f->stream));
+    if (!on_device) FCU(f, cudaStreamSynchronize(f->stream));
+    v.set2 = true;
     return 0;
 }
 

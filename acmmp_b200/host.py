@@ -458,6 +458,23 @@ class Fusion:
         self.num_points = n.value
         return n.value
 
+    def set_view_second(self, view, depth2, normal2, on_device=False):
+        """the second (depth, normal) set of a view, for run_prior_aware"""
+        if on_device:
+            ptrs = [C.c_void_p(int(depth2)), C.c_void_p(int(normal2))]
+        else:
+            keep = [L.f32(depth2), L.f32(normal2)]
+            ptrs = [C.c_void_p(a.ctypes.data) for a in keep]
+        self._ck(self._lib.acmmp_fusion_set_view_second(self._f, view, ptrs[0], ptrs[1], int(on_device)), "fusion_set_view_second")
+
+    def run_prior_aware(self, consistency_scalar=0.3, num_consistent_thresh=1, single_match_penalty=1):
+        """RunPriorAwareFusion (acmmp_definitions.cpp:575-826) on the device"""
+        n = C.c_int64()
+        self._ck(self._lib.acmmp_fusion_run_prior_aware(self._f, float(consistency_scalar), int(num_consistent_thresh),
+                                                        int(single_match_penalty), C.byref(n)), "fusion_run_prior_aware")
+        self.num_points = n.value
+        return n.value
+
     def points(self):
         pts = np.empty((self.num_points, 9), np.float32)
         per = (C.c_int64 * self.n)()
@@ -484,6 +501,21 @@ def RunFusion(cams, pairs, depths, normals, colors=None, masks=None, consistency
         for v in range(len(cams)):
             f.set_view(v, depths[v], normals[v], None if colors is None else colors[v], None if masks is None else masks[v])
         f.run(consistency_scalar, con_num_thresh)
+        return f.points()
+    finally:
+        f.close()
+
+
+def RunPriorAwareFusion(cams, pairs, depths, normals, depths2, normals2, colors=None, masks=None, consistency_scalar=0.3,
+                        num_consistent_thresh=1, single_match_penalty=1, device=0):
+    """RunPriorAwareFusion with in-memory maps (set 0 = the reference's fusion-folder maps, set 1 = the run's
+    own): returns (points[N, 9], per-view accepted counts)."""
+    f = Fusion(cams, pairs, device)
+    try:
+        for v in range(len(cams)):
+            f.set_view(v, depths[v], normals[v], None if colors is None else colors[v], None if masks is None else masks[v])
+            f.set_view_second(v, depths2[v], normals2[v])
+        f.run_prior_aware(consistency_scalar, num_consistent_thresh, single_match_penalty)
         return f.points()
     finally:
         f.close()

@@ -146,6 +146,15 @@ public:
         check(acmmp_fusion_run(f_, consistency_scalar, con_num_thresh, &n));
         return n;
     }
+    // second (depth, normal) set of a view + RunPriorAwareFusion (acmmp_definitions.cpp:575-826)
+    void SetViewSecond(int view, const float *depth2, const float *normal2, bool on_device) {
+        check(acmmp_fusion_set_view_second(f_, view, depth2, normal2, on_device ? 1 : 0));
+    }
+    int64_t RunPriorAware(float consistency_scalar, int num_consistent_thresh, int single_match_penalty) {
+        int64_t n = 0;
+        check(acmmp_fusion_run_prior_aware(f_, consistency_scalar, num_consistent_thresh, single_match_penalty, &n));
+        return n;
+    }
     void GetPoints(std::vector<float> &points9, std::vector<int64_t> &per_view, int64_t n, int n_views) {
         points9.resize((size_t)n * 9);
         per_view.resize(n_views);

@@ -61,6 +61,7 @@ EXPORTS = [
     "acmmp_count_ncc", "acmmp_ncc_count", "acmmp_scan_count_ncc", "acmmp_scan_ncc_count",
     "acmmp_fusion_create", "acmmp_fusion_destroy", "acmmp_fusion_last_error", "acmmp_fusion_set_view", "acmmp_fusion_run",
     "acmmp_fusion_get_points", "acmmp_fusion_get_mask", "acmmp_fusion_stats",
+    "acmmp_fusion_set_view_second", "acmmp_fusion_run_prior_aware",
     "acmmp_jpeg_info", "acmmp_decode_jpeg", "acmmp_jpeg_last_error",
     "acmmp_pair_scores", "acmmp_pairs_last_error",
     "acmmp_scan_create", "acmmp_scan_destroy", "acmmp_scan_last_error", "acmmp_scan_set_image",
@@ -155,6 +156,8 @@ def load():
     lib.acmmp_fusion_last_error.restype = C.c_char_p
     lib.acmmp_fusion_set_view.argtypes = [vp, C.c_int, vp, vp, vp, vp, C.c_int]
     lib.acmmp_fusion_run.argtypes = [vp, C.c_float, C.c_int, C.POINTER(C.c_int64)]
+    lib.acmmp_fusion_set_view_second.argtypes = [vp, C.c_int, vp, vp, C.c_int]
+    lib.acmmp_fusion_run_prior_aware.argtypes = [vp, C.c_float, C.c_int, C.c_int, C.POINTER(C.c_int64)]
     lib.acmmp_fusion_get_points.argtypes = [vp, vp, C.c_int64, C.POINTER(C.c_int64)]
     lib.acmmp_fusion_get_mask.argtypes = [vp, C.c_int, vp]
     lib.acmmp_fusion_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int32)]

@@ -3,8 +3,8 @@
 // runs the multi-scale schedule (photometric + planar prior, geom x2 per scale) resident on
 // the device, writes <dense_folder><output_dir>/2333_%08d/{depths,depths_geom,normals,costs}.dmb
 // and fuses into ACMMP_model.ply.  Hand-rolled flag parser (Boost is not in this image).
-// Not supported (out of scope): --prior, --multi_fusion, --force_fusion,
-// --single_match_penalty - they need the external prior package that is not in the reference tree.
+// --force_fusion / --multi_fusion [DIR] / --single_match_penalty N select the prior-aware fusion
+// (main_ACMMP.cpp:178-189): map set 0 is read from <dense_folder><DIR>/2333_*/, set 1 is this run's.
 #include <sys/stat.h>
 
 #include <cstdio>
@@ -38,9 +38,10 @@ static bool find_image(const std::string &folder, int id, Map<uint8_t> &im, std:
 int main(int argc, char **argv) {
     std::string dense_folder, output_dir = "/ACMMP", mask_dir = " ", image_dir = "/images";
     float consistency_scalar = 0.3f;
-    int num_consistent_thresh = 1, device = 0;
+    int num_consistent_thresh = 1, single_match_penalty = 0, device = 0;
     unsigned long long seed = 0;
-    bool fuse = true;
+    bool fuse = true, force_fusion = false, multi_fusion = false, prior = false;
+    std::string fusion_dir = "/ACMMP";
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto value = [&](const char *name) -> const char * {
@@ -52,7 +53,8 @@ int main(int argc, char **argv) {
         };
         if (a == "-h" || a == "--help") {
             printf("usage: acmmp_main <dense_folder> [--output_dir /ACMMP] [-f|--fuse_thresh 0.3] [--num_consistent_thresh 1]\n"
-                   "                  [--mask_dir DIR] [--image_override DIR] [--device 0] [--seed N] [--no_fusion]\n");
+                   "                  [--mask_dir DIR] [--image_override DIR] [--device 0] [--seed N] [--no_fusion]\n"
+                   "                  [--force_fusion] [--multi_fusion [/DIR]] [--single_match_penalty N] [-p|--prior]\n");
             return 1;
         } else if (a == "--dense_folder") dense_folder = value("--dense_folder");
         else if (a == "--output_dir") output_dir = value("--output_dir");
@@ -63,10 +65,13 @@ int main(int argc, char **argv) {
         else if (a == "--device") device = atoi(value("--device"));
         else if (a == "--seed") seed = strtoull(value("--seed"), nullptr, 10);
         else if (a == "--no_fusion") fuse = false;
-        else if (a == "-p" || a == "--prior" || a == "--multi_fusion" || a == "--force_fusion" || a == "--single_match_penalty") {
-            fprintf(stderr, "%s: prior-aware modes need the external prior package; not supported\n", a.c_str());
-            return EXIT_FAILURE;
-        } else if (a[0] != '-') dense_folder = a;
+        else if (a == "--force_fusion") force_fusion = true;
+        else if (a == "--multi_fusion") {   // implicit value "/ACMMP" (main_ACMMP.cpp:31)
+            multi_fusion = true;
+            if (i + 1 < argc && argv[i + 1][0] == '/') fusion_dir = argv[++i];
+        } else if (a == "--single_match_penalty") single_match_penalty = atoi(value("--single_match_penalty"));
+        else if (a == "-p" || a == "--prior") prior = true;
+        else if (a[0] != '-') dense_folder = a;
         else {
             fprintf(stderr, "unknown option %s\n", a.c_str());
             return EXIT_FAILURE;
@@ -152,6 +157,8 @@ int main(int argc, char **argv) {
         }
         printf("depth maps written to %s\n", output_folder.c_str());
         if (fuse) {
+            const bool prior_aware = (prior && multi_fusion) || force_fusion;   // main_ACMMP.cpp:181
+            const std::string fusion_folder = dense_folder + fusion_dir;
             Fusion fusion(cams_out, pairs, device);
             for (int i = 0; i < n; ++i) {
                 Map<uint8_t> color;   // colour read for the point colours (acmmp_definitions.cpp:857)
@@ -185,14 +192,29 @@ int main(int argc, char **argv) {
                 // colour and mask come from the host, so the maps take the same way (one flag per call)
                 Map<float> hd, hn;
                 scan.GetView(i, &hd, &hn, nullptr);
-                fusion.SetView(i, hd.data.data(), hn.data.data(), color.data.data(), mask.empty() ? nullptr : mask.data(), false);
+                if (prior_aware) {
+                    // set 0 = the maps of the fusion folder, set 1 = this run's (acmmp_definitions.cpp:607-643)
+                    const std::string folder = fusion_folder + "/2333_" + id_name(problems[i].ref_image_id, "");
+                    Map<float> d0, n0;
+                    if (readDepthDmb(folder + "/depths_geom.dmb", d0) || readNormalDmb(folder + "/normals.dmb", n0) ||
+                        d0.cols != cams_out[i].width || d0.rows != cams_out[i].height) {
+                        fprintf(stderr, "cannot read the maps of image %d under %s\n", problems[i].ref_image_id, folder.c_str());
+                        return EXIT_FAILURE;
+                    }
+                    fusion.SetView(i, d0.data.data(), n0.data.data(), color.data.data(), mask.empty() ? nullptr : mask.data(), false);
+                    fusion.SetViewSecond(i, hd.data.data(), hn.data.data(), false);
+                } else {
+                    fusion.SetView(i, hd.data.data(), hn.data.data(), color.data.data(), mask.empty() ? nullptr : mask.data(), false);
+                }
             }
-            const int64_t count = fusion.Run(consistency_scalar, num_consistent_thresh);
+            const int64_t count = prior_aware ? fusion.RunPriorAware(consistency_scalar, num_consistent_thresh, single_match_penalty)
+                                              : fusion.Run(consistency_scalar, num_consistent_thresh);
             std::vector<float> pts;
             std::vector<int64_t> per_view;
             fusion.GetPoints(pts, per_view, count, n);
             for (int i = 0; i < n; ++i) printf("Fusing image %08d... approved %lld pts\n", i, (long long)per_view[i]);
-            if (!StoreColorPlyFileBinaryPointCloud(output_folder + "/ACMMP_model.ply", pts.data(), (size_t)count)) {
+            if (!StoreColorPlyFileBinaryPointCloud(output_folder + (prior_aware ? "/ACMMP_prior_model.ply" : "/ACMMP_model.ply"), pts.data(),
+                                                   (size_t)count)) {
                 fprintf(stderr, "cannot write the PLY\n");
                 return EXIT_FAILURE;
             }

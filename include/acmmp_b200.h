@@ -355,6 +355,16 @@ int acmmp_fusion_get_mask(acmmp_fusion *f, int view, uint8_t *mask);
 /* device ms of the last run: {score, greedy fixed point, compaction}; fixed-point rounds per view */
 int acmmp_fusion_stats(acmmp_fusion *f, double ms[3], int32_t *rounds_per_view);
 
+/* Prior-aware fusion (RunPriorAwareFusion, /root/reference/src/acmmp_definitions.cpp:443-826; the
+ * reference's --multi_fusion / --force_fusion modes, main_ACMMP.cpp:178-189).  Every view carries a
+ * second (depth, normal) set besides the one of acmmp_fusion_set_view: set 0 is what the reference
+ * reads from its fusion folder, set 1 what it reads from the run's own output folder (:607-643).
+ * A pixel tries both hypotheses against both maps of every source view; the one with more consistent
+ * sources wins, a hypothesis passing alone needs single_match_penalty more consistent sources. */
+int acmmp_fusion_set_view_second(acmmp_fusion *f, int view, const float *depth2, const float *normal3_2, int on_device);
+int acmmp_fusion_run_prior_aware(acmmp_fusion *f, float consistency_scalar, int num_consistent_thresh,
+                                 int single_match_penalty, int64_t *num_points);
+
 /* ==== JPEG decode on the device (nvJPEG) ======================================
  * What the reference gets from cv::imread: mode 0 = IMREAD_GRAYSCALE (the luma
  * plane, ACMMP.cpp:534-541), mode 1 = IMREAD_COLOR (interleaved BGR,

@@ -131,3 +131,36 @@ def test_cli_reads_real_jpegs(tmp_path):
     assert (np.abs(depth - gt)[8:-8, 8:-8] / gt[8:-8, 8:-8] < 0.01).mean() >= 0.9
     xyz_n, col = read_ply(os.path.join(dense, "OUT", "ACMMP_model.ply"))
     assert len(xyz_n) > 50000 and col.max() > 0
+
+
+@pytest.mark.skipif(not refbind.host_available(), reason="oracle/_ref/libacmmp_ref_host*.so not built")
+def test_cli_prior_aware_fusion_against_reference(cli_run):
+    """--force_fusion --multi_fusion /ACMMP: a second run (another seed, output /ACMMP_B) fused with the
+    first run's maps; the reference's own RunPriorAwareFusion then reads the same two folders."""
+    sc, dense, ids, _ = cli_run
+    n = len(ids)
+    out = subprocess.run([EXE, dense, "--seed", "9", "--output_dir", "/ACMMP_B", "--force_fusion", "--multi_fusion", "/ACMMP",
+                          "--single_match_penalty", "1", "--num_consistent_thresh", "2"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    outdir = os.path.join(dense, "ACMMP_B")
+    ply = os.path.join(outdir, "ACMMP_prior_model.ply")
+    xyz_n, col = read_ply(ply)
+    assert len(xyz_n) > 50000 and not os.path.exists(os.path.join(outdir, "ACMMP_model.ply"))
+    shutil.copy(ply, os.path.join(outdir, "ours_prior.ply"))
+    import ctypes as C
+    lib = C.CDLL(refbind.REF_HOST_PATHS["ieee"])
+    lib.ref_host_run_prior_fusion.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                              C.POINTER(C.c_int), C.c_int, C.c_float, C.c_int, C.c_int]
+    offs, flat = [0], []
+    for p in sc["pairs"]:
+        flat += [ids[j] for j in p]
+        offs.append(len(flat))
+    rc = lib.ref_host_run_prior_fusion(dense.encode(), outdir.encode(), os.path.join(dense, "ACMMP").encode(), n, (C.c_int * n)(*ids),
+                                       (C.c_int * (n + 1))(*offs), (C.c_int * len(flat))(*flat), 1, 0.3, 2, 1)
+    assert rc == 0
+    ref_xyz_n, ref_col = read_ply(ply)
+    assert abs(len(ref_xyz_n) - len(xyz_n)) <= max(1, int(1e-3 * len(ref_xyz_n))), (len(ref_xyz_n), len(xyz_n))
+    if len(ref_xyz_n) == len(xyz_n):
+        same = (ref_xyz_n.view(np.uint32) == xyz_n.view(np.uint32)).all(1).mean()
+        assert same >= 0.999, same
+        assert (ref_col == col).all()
