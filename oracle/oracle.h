@@ -109,6 +109,10 @@ long orc_prior_fusion(int n, const orc_camera *cams, const float *const *depths,
                       const uint8_t *const *masks0, const int *pair_offsets, const int *pair_ids, float consistency_scalar,
                       int num_consistent_thresh, int single_match_penalty, float *points, long capacity);
 
+/* seeded hypotheses from 16-bit prior images (pSampler::GetPriorPlaneEstimate, acmmp_definitions.cpp:98-177) */
+void orc_prior_planes_from_maps(const orc_camera *cam, const uint16_t *depth16, const uint16_t *normal16, int prows, int pcols,
+                                int rows, int cols, float *planes4);
+
 #ifdef __cplusplus
 }
 #endif

@@ -48,3 +48,18 @@ extern "C" int ref_host_run_prior_fusion(const char *dense_folder, const char *o
                         single_match_penalty, std::string(" "));
     return 0;
 }
+
+// pSampler::GetPriorPlaneEstimate (acmmp_definitions.cpp:7-177): the seeded hypotheses of view `cam_num`
+// from <dense_folder>priors/{depths,normals}/%08d.png (16-bit; the test writes the raw container).
+// `cam` has the layout of the reference's Camera.  Returns -1 when pSampler finds no priors.
+extern "C" int ref_host_prior_planes(const char *dense_folder, int ncams, int cam_num, const void *cam, int rows, int cols,
+                                     float *planes4) {
+    pSampler sampler(std::string(dense_folder), ncams);
+    if (!sampler.confirm_using_prior()) return -1;
+    Camera c;
+    memcpy(&c, cam, sizeof c);
+    std::unique_ptr<float4> planes = sampler.GetPriorPlaneEstimate(cam_num, c, rows, cols);
+    memcpy(planes4, planes.get(), sizeof(float4) * (size_t)rows * cols);
+    delete[] planes.release();
+    return 0;
+}

@@ -24,6 +24,9 @@ typedef unsigned char uchar;
 #define CV_8U 0
 #define CV_8UC1 0
 #define CV_8UC3 16
+#define CV_16U 2
+#define CV_16UC1 2
+#define CV_16UC3 18
 #define CV_32F 5
 #define CV_32FC1 5
 #define CV_32FC3 21
@@ -74,7 +77,7 @@ struct Mat {
     size_t step[2] = {0, 0};
     std::shared_ptr<std::vector<unsigned char>> store;
 
-    static size_t elem_size(int type) { return (size_t)(CV_MAT_DEPTH(type) == CV_32F ? 4 : 1) * CV_MAT_CN(type); }
+    static size_t elem_size(int type) { return (size_t)(CV_MAT_DEPTH(type) == CV_32F ? 4 : CV_MAT_DEPTH(type) == CV_16U ? 2 : 1) * CV_MAT_CN(type); }
     void create(int r, int c, int type) {
         rows = r; cols = c; type_ = type;
         store = std::make_shared<std::vector<unsigned char>>((size_t)r * c * elem_size(type), 0);
@@ -116,6 +119,16 @@ struct Mat {
         const int dtype = (CV_MAT_DEPTH(rtype)) | ((cn - 1) << 3);
         Mat out(rows, cols, dtype);
         const size_t n = total() * cn;
+        if (CV_MAT_DEPTH(type_) == CV_16U && CV_MAT_DEPTH(rtype) == CV_32F) {
+            // 16-bit -> float with scale: OpenCV's cvtScale works in float for this pair (src * (float)alpha + (float)beta)
+            const float fa = (float)alpha, fb = (float)beta;
+            for (size_t i = 0; i < n; ++i) {
+                const float prod = (float)reinterpret_cast<const unsigned short *>(data)[i] * fa;
+                reinterpret_cast<float *>(out.data)[i] = prod + fb;
+            }
+            dst = out;
+            return;
+        }
         for (size_t i = 0; i < n; ++i) {
             const double v = (CV_MAT_DEPTH(type_) == CV_32F ? (double)reinterpret_cast<const float *>(data)[i] : (double)data[i]) * alpha + beta;
             if (CV_MAT_DEPTH(rtype) == CV_32F) reinterpret_cast<float *>(out.data)[i] = (float)v;
@@ -159,14 +172,30 @@ inline Mat operator/(const Mat &a, double v) {
 }
 
 // imread: OpenCV's codecs are not available.  The tests write images as a raw container
-// under the file name the reference expects: "ACMRAW1\n" rows cols channels "\n" + bytes.
+// under the file name the reference expects: "ACMRAW1\n" rows cols channels "\n" + bytes;
+// "ACMRAW2" holds 16-bit little-endian samples (the prior PNGs of pSampler), returned as they are
+// for flags < 0 (IMREAD_UNCHANGED) and reduced to 8 bits otherwise.
 inline Mat imread(const std::string &path, int flags = IMREAD_COLOR) {
     Mat out;
     FILE *f = fopen(path.c_str(), "rb");
     if (!f) return out;
     char magic[16] = {0};
     int r = 0, c = 0, cn = 0;
-    if (fscanf(f, "%15s %d %d %d", magic, &r, &c, &cn) == 4 && std::string(magic) == "ACMRAW1" && fgetc(f) == '\n') {
+    if (fscanf(f, "%15s %d %d %d", magic, &r, &c, &cn) != 4 || fgetc(f) != '\n') {
+        fclose(f);
+        return out;
+    }
+    if (std::string(magic) == "ACMRAW2") {
+        Mat raw(r, c, cn == 3 ? CV_16UC3 : CV_16UC1);
+        if (fread(raw.data, 2, (size_t)r * c * cn, f) == (size_t)r * c * cn) {
+            if (flags < 0) {
+                out = raw;
+            } else {
+                out.create(r, c, cn == 3 ? CV_8UC3 : CV_8UC1);
+                for (size_t i = 0; i < (size_t)r * c * cn; ++i) out.data[i] = (unsigned char)(reinterpret_cast<unsigned short *>(raw.data)[i] >> 8);
+            }
+        }
+    } else if (std::string(magic) == "ACMRAW1") {
         Mat raw(r, c, cn == 3 ? CV_8UC3 : CV_8UC1);
         if (fread(raw.data, 1, (size_t)r * c * cn, f) == (size_t)r * c * cn) {
             if (flags == IMREAD_GRAYSCALE && cn == 3) {

@@ -327,3 +327,44 @@ long orc_prior_fusion(int n, const orc_camera *cams, const float *const *depths,
     free(masks);
     return count;
 }
+
+/* ---- pSampler::GetPriorPlaneEstimate, acmmp_definitions.cpp:98-177 (seeded mode, `-p`) ------------
+ * depth16 / normal16: the 16-bit prior images as cv::imread(path, -1) returns them (prows x pcols; the
+ * normal image's three channels in stored order: channel 0 -> x).  Depth = v * (dmax - dmin) / 65535 +
+ * dmin, normal = v * 2 / 65536 - 1 (cv::Mat::convertTo, float arithmetic for 16-bit sources); sampled
+ * at (i * scale, j * scale), scale = prows / rows (:133).  The plane is the normal flipped to face the
+ * camera, "normalised" by normVec3 - which MULTIPLIES by the length (:34-41), kept - and the distance
+ * of the back-projected pixel to the origin.  Pinned against the reference's own function
+ * (oracle/ref_host_harness.cpp: ref_host_prior_planes, IEEE build) in tests/test_seeded.py. */
+void orc_prior_planes_from_maps(const orc_camera *cam, const uint16_t *depth16, const uint16_t *normal16, int prows, int pcols,
+                                int rows, int cols, float *planes4) {
+    (void)pcols;
+    const float dist = cam->depth_max - cam->depth_min;
+    const float range = dist / 65535.0f;
+    const float na = (float)(2.0 / 65536.0), nb = -1.0f;
+    const int scale = prows / rows;
+    for (int i = 0; i < rows; ++i)
+        for (int j = 0; j < cols; ++j) {
+            const size_t at = (size_t)(i * scale) * pcols + (size_t)j * scale;
+            const float dprod = (float)depth16[at] * range;
+            const float depth = dprod + cam->depth_min;
+            float n[3];
+            for (int k = 0; k < 3; ++k) {
+                const float prod = (float)normal16[3 * at + k] * na;
+                n[k] = prod + nb;
+            }
+            float X[3];
+            X[0] = depth * (j - cam->K[2]) / cam->K[0];
+            X[1] = depth * (i - cam->K[5]) / cam->K[4];
+            X[2] = depth;
+            const float norm = (float)sqrt(X[0] * X[0] + X[1] * X[1] + X[2] * X[2]);
+            const float v0 = X[0] / norm, v1 = X[1] / norm, v2 = X[2] / norm;
+            const float dot = n[0] * v0 + n[1] * v1 + n[2] * v2;
+            if (dot > 0.0f) { n[0] = -n[0]; n[1] = -n[1]; n[2] = -n[2]; }
+            const float len = sqrtf(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+            n[0] *= len; n[1] *= len; n[2] *= len;
+            float *o = planes4 + 4 * ((size_t)i * cols + j);
+            o[0] = n[0]; o[1] = n[1]; o[2] = n[2];
+            o[3] = -(n[0] * X[0] + n[1] * X[1] + n[2] * X[2]);
+        }
+}

@@ -88,6 +88,9 @@ def load():
     lib.orc_prior_fusion.argtypes = [C.c_int, C.POINTER(OrcCamera), C.POINTER(fp), C.POINTER(fp), C.POINTER(fp), C.POINTER(fp),
                                      u8pp, u8pp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_float, C.c_int, C.c_int, fp, C.c_long]
     lib.orc_prior_fusion.restype = C.c_long
+    u16p = C.POINTER(C.c_uint16)
+    lib.orc_prior_planes_from_maps.argtypes = [C.POINTER(OrcCamera), u16p, u16p, C.c_int, C.c_int, C.c_int, C.c_int, fp]
+    lib.orc_prior_planes_from_maps.restype = None
     i32p = C.POINTER(C.c_int32)
     lib.orc_support_points.argtypes = [fp, C.c_int, C.c_int, i32p]
     lib.orc_prior_from_triangles.argtypes = [C.POINTER(OrcCamera), fp, C.c_int, C.c_int, i32p, C.c_int, C.c_float, C.c_float, fp, fp, up]
@@ -314,6 +317,19 @@ def prior_fusion(cams, depths, normals, depths2, normals2, pairs, consistency_sc
                                   ids.ctypes.data_as(C.POINTER(C.c_int)), consistency_scalar, num_consistent_thresh,
                                   single_match_penalty, _fp(pts), cap)
     return int(cnt), pts[:cnt]
+
+
+def prior_planes_from_maps(cam, depth16, normal16, rows, cols):
+    """pSampler::GetPriorPlaneEstimate restatement -> (rows, cols, 4) planes (camera-frame normal, distance)."""
+    d = np.ascontiguousarray(depth16, np.uint16)
+    n = np.ascontiguousarray(normal16, np.uint16)
+    assert n.shape == d.shape + (3,)
+    out = np.zeros((rows, cols, 4), np.float32)
+    oc = to_orc_camera(cam)
+    u16p = C.POINTER(C.c_uint16)
+    load().orc_prior_planes_from_maps(C.byref(oc), d.ctypes.data_as(u16p), n.ctypes.data_as(u16p), d.shape[0], d.shape[1], rows, cols,
+                                      _fp(out))
+    return out
 
 
 def support_points(costs):

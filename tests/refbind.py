@@ -301,6 +301,32 @@ def host_prior_fusion(workdir, cams, depths, normals, depths2, normals2, colors,
     return _read_ply_points(os.path.join(out, "ACMMP_prior_model.ply"))
 
 
+def write_prior_images(dense, index, depth16, normal16):
+    """<dense>/priors/{depths,normals}/%08d.png as the 16-bit raw container of oracle/ref_stub"""
+    for sub, arr in (("depths", depth16), ("normals", normal16)):
+        folder = os.path.join(dense, "priors", sub)
+        os.makedirs(folder, exist_ok=True)
+        a = np.ascontiguousarray(arr, np.uint16)
+        cn = 1 if a.ndim == 2 else a.shape[2]
+        with open(os.path.join(folder, "%08d.png" % index), "wb") as f:
+            f.write(b"ACMRAW2 %d %d %d\n" % (a.shape[0], a.shape[1], cn) + a.astype("<u2").tobytes())
+
+
+def host_prior_planes(dense, ncams, index, cam, rows, cols, build="ieee"):
+    """The reference's own pSampler::GetPriorPlaneEstimate on <dense>/priors (written by write_prior_images)."""
+    key = "planes_" + build
+    if key not in _ref_host:
+        lib = C.CDLL(REF_HOST_PATHS[build])
+        lib.ref_host_prior_planes.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]
+        _ref_host[key] = lib
+    out = np.zeros((rows, cols, 4), np.float32)
+    c = cam.copy() if hasattr(cam, "copy") else cam
+    rc = _ref_host[key].ref_host_prior_planes((dense.rstrip("/") + "/").encode(), ncams, index, C.byref(c), rows, cols,
+                                              out.ctypes.data_as(C.POINTER(C.c_float)))
+    assert rc == 0, rc
+    return out
+
+
 # ---- the reference PROGRAM (kernels + host class + ProcessProblem + JBU + RunFusion) -----------
 REF_FULL_PATH = os.path.join(_REF_DIR, "libacmmp_ref_full.so")
 _ref_full = None
