@@ -22,10 +22,10 @@ all: $(LIB) oracle cli
 cli: build/acmmp_main build/io_selftest
 build/io_selftest: cli/io_selftest.cpp $(wildcard acmmp_b200/host/*.hpp) include/acmmp_b200.h
 	@mkdir -p build
-	$(REF_CXX) -O2 -std=c++17 -Wall -o $@ cli/io_selftest.cpp
+	$(REF_CXX) -O2 -std=c++17 -Wall -o $@ cli/io_selftest.cpp -lz
 build/acmmp_main: cli/acmmp_main.cpp $(wildcard acmmp_b200/host/*.hpp) include/acmmp_b200.h $(LIB)
 	@mkdir -p build
-	$(REF_CXX) -O2 -std=c++17 -Wall -o $@ cli/acmmp_main.cpp -Lacmmp_b200 -lacmmp_b200 -Wl,-rpath,'$$ORIGIN/../acmmp_b200' -L$(CUDA_LIB) -lcudart
+	$(REF_CXX) -O2 -std=c++17 -Wall -o $@ cli/acmmp_main.cpp -Lacmmp_b200 -lacmmp_b200 -Wl,-rpath,'$$ORIGIN/../acmmp_b200' -L$(CUDA_LIB) -lcudart -lz
 
 # fusion.cu restates host code of the reference (IEEE float / double): no fast math, no contraction
 FUSIONFLAGS := -O3 -std=c++17 $(ARCH) -lineinfo -fmad=false -Xcompiler -fPIC
@@ -38,8 +38,12 @@ build/pairs.o: $(CSRC)/pairs.cu include/acmmp_b200.h
 	@mkdir -p build
 	$(NVCC) $(FUSIONFLAGS) -c -o $@ $(CSRC)/pairs.cu
 
-$(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o -lnvjpeg_static -lculibos -lcudart
+build/seeded.o: $(CSRC)/seeded.cu $(CSRC)/kernels.h include/acmmp_b200.h
+	@mkdir -p build
+	$(NVCC) $(FUSIONFLAGS) -c -o $@ $(CSRC)/seeded.cu
+
+$(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o build/seeded.o $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o build/seeded.o -lnvjpeg_static -lculibos -lcudart
 
 oracle: oracle/liboracle.so
 
@@ -78,5 +82,5 @@ oracle/_ref/libacmmp_ref_host_ieee.so: $(REF_HOST_SRC)
 	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
 
 clean:
-	rm -f $(LIB) build/fusion.o build/pairs.o oracle/liboracle.so oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so
+	rm -f $(LIB) build/fusion.o build/pairs.o build/seeded.o oracle/liboracle.so oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so
 .PHONY: all oracle ref cli clean

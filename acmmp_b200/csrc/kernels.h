@@ -64,6 +64,9 @@ cudaError_t launch_jbu_depth(const float *image, int w, int h, const float *sdep
 cudaError_t launch_resize_linear(const float *src, int sw, int sh, float *dst, int dw, int dh, cudaStream_t st);
 cudaError_t launch_pad_replicate(const float *src, int w, int h, float *dst, int W, int H, cudaStream_t st);
 cudaError_t launch_fp32_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
+// seeded.cu (IEEE build): seeded hypotheses of one view at the current level from its 16-bit prior images
+cudaError_t launch_prior_maps_to_planes(const acmmp_camera &cam, const uint16_t *depth16, const uint16_t *normal16, int prows,
+                                        int pcols, int rows, int cols, float4 *planes, cudaStream_t st);
 cudaError_t launch_tex_sample(cudaTextureObject_t tex, const float *xs, const float *ys, int n, float *out, cudaStream_t st);
 cudaError_t launch_tex_peak(cudaTextureObject_t tex, int w, int h, int layers, int blocks, int threads, int iters, int mode,
                             float *scratch, cudaStream_t st);

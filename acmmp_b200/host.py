@@ -218,6 +218,21 @@ def resize_linear(image, new_w, new_h, device=0):
     return out
 
 
+def prior_planes_from_maps(cam, depth16, normal16, rows, cols, device=0):
+    """pSampler::GetPriorPlaneEstimate (acmmp_definitions.cpp:98-177) on the device -> (rows, cols, 4) planes"""
+    lib = L.load()
+    d = np.ascontiguousarray(depth16, np.uint16)
+    n = np.ascontiguousarray(normal16, np.uint16)
+    out = np.empty((rows, cols, 4), np.float32)
+    u16p = C.POINTER(C.c_uint16)
+    c = cam.copy()
+    rc = lib.acmmp_prior_planes_from_maps(device, C.byref(c), d.ctypes.data_as(u16p), n.ctypes.data_as(u16p), d.shape[0], d.shape[1],
+                                          rows, cols, L.fptr(out))
+    if rc != 0:
+        raise L.AcmmpError(f"acmmp_prior_planes_from_maps failed ({rc}): {lib.acmmp_seeded_last_error().decode()}")
+    return out
+
+
 def tex_sample(image, xs, ys, device=0):
     """Bilinear fetches of `image` at (xs, ys) through the views' texture set-up (ACMMP.cpp:646-663)."""
     lib = L.load()
@@ -373,6 +388,20 @@ class Scan:
         a, b = C.c_double(), C.c_double()
         self._ck(self._lib.acmmp_scan_host_stats(self._s, C.byref(a), C.byref(b)), "host_stats")
         return {"prior_host_ms": a.value, "wait_ms": b.value}
+
+    def set_prior_maps(self, view, depth16=None, normal16=None):
+        """seeded mode (-p): the 16-bit prior images of a view as cv::imread(path, -1) returns them
+        (pSampler, acmmp_definitions.cpp:98-131); None, None removes them"""
+        u16p = C.POINTER(C.c_uint16)
+        if depth16 is None and normal16 is None:
+            self._ck(self._lib.acmmp_scan_set_prior_maps(self._s, view, None, None, 0, 0), "set_prior_maps")
+            return
+        d = np.ascontiguousarray(depth16, np.uint16)
+        n = np.ascontiguousarray(normal16, np.uint16)
+        if n.shape != d.shape + (3,):
+            raise ValueError("normal16 must be (rows, cols, 3) for depth16 (rows, cols)")
+        self._ck(self._lib.acmmp_scan_set_prior_maps(self._s, view, d.ctypes.data_as(u16p), n.ctypes.data_as(u16p), d.shape[0], d.shape[1]),
+                 "set_prior_maps")
 
     def count_ncc(self, enable=True):
         """switch the device-side count of NCC evaluations on / off (instrumentation)"""

@@ -98,6 +98,19 @@ public:
     Scan(const Scan &) = delete;
     Scan &operator=(const Scan &) = delete;
     void SetImage(int view, const Map<float> &gray) { check(acmmp_scan_set_image(s_, view, gray.data.data(), 0)); check(acmmp_scan_sync(s_)); }
+    // seeded mode (-p): the 16-bit prior images of a view in cv::imread(path, -1) order (pSampler, acmmp_definitions.cpp:98-131)
+    void SetPriorMaps(int view, const Map<uint16_t> &depth16, const Map<uint16_t> &normal16) {
+        if (depth16.channels != 1 || normal16.channels < 3 || normal16.rows != depth16.rows || normal16.cols != depth16.cols)
+            throw std::runtime_error("prior images: need a 1-channel depth and a 3-channel normal image of the same size");
+        if (normal16.channels == 3) {
+            check(acmmp_scan_set_prior_maps(s_, view, depth16.data.data(), normal16.data.data(), depth16.rows, depth16.cols));
+            return;
+        }
+        std::vector<uint16_t> n3((size_t)normal16.rows * normal16.cols * 3);   // drop the alpha channel
+        for (size_t p = 0; p < (size_t)normal16.rows * normal16.cols; ++p)
+            for (int k = 0; k < 3; ++k) n3[3 * p + k] = normal16.data[p * normal16.channels + k];
+        check(acmmp_scan_set_prior_maps(s_, view, depth16.data.data(), n3.data(), depth16.rows, depth16.cols));
+    }
     int NumLevels() const { return acmmp_scan_num_levels(s_); }
     void BeginLevel(int level) { check(acmmp_scan_begin_level(s_, level)); }
     void RunStage(int stage, uint64_t seed) { check(acmmp_scan_run_stage(s_, stage, seed)); }

@@ -7,11 +7,16 @@
 #include <cfloat>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <fstream>
 #include <string>
 #include <vector>
 
 #include "../../include/acmmp_b200.h"
+#ifdef ACMMP_IO_WITH_PNG
+#include <zlib.h>   // link with -lz
+#endif
 
 namespace acmmp_b200 {
 
@@ -98,6 +103,84 @@ inline int writeDepthDmb(const std::string &p, const Map<float> &depth) { return
 inline int writeNormalDmb(const std::string &p, const Map<float> &normal) { return writeDmb(p, normal.data.data(), normal.rows, normal.cols, 3); }
 inline int readDepthDmb(const std::string &p, Map<float> &depth) { return readDmb(p, depth); }
 inline int readNormalDmb(const std::string &p, Map<float> &normal) { return readDmb(p, normal); }
+
+#ifdef ACMMP_IO_WITH_PNG
+// PNG (8 / 16 bit; grey, grey + alpha, RGB, RGBA; not interlaced, no palette) decoded with zlib into
+// 16-bit samples in cv::imread(path, -1) order: colour channels as B, G, R (, A).  Used for the 16-bit
+// prior images of the seeded mode (acmmp_definitions.cpp:104-105) and for 8-bit masks (:886-902).
+inline bool ReadPng16(const std::string &path, Map<uint16_t> &out, int *bit_depth = nullptr, std::string *err = nullptr) {
+    auto fail = [&](const std::string &why) {
+        if (err) *err = path + ": " + why;
+        return false;
+    };
+    FILE *f = fopen(path.c_str(), "rb");
+    if (!f) return fail("cannot open");
+    fseek(f, 0, SEEK_END);
+    const long n = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    std::vector<uint8_t> buf((size_t)(n > 0 ? n : 0));
+    const bool got = n > 0 && fread(buf.data(), 1, buf.size(), f) == buf.size();
+    fclose(f);
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
+    if (!got || buf.size() < 8 || memcmp(buf.data(), sig, 8) != 0) return fail("not a PNG file");
+    auto be32 = [&](size_t at) { return ((uint32_t)buf[at] << 24) | ((uint32_t)buf[at + 1] << 16) | ((uint32_t)buf[at + 2] << 8) | buf[at + 3]; };
+    uint32_t w = 0, h = 0;
+    int depth = 0, ctype = -1;
+    std::vector<uint8_t> idat;
+    for (size_t pos = 8; pos + 12 <= buf.size();) {
+        const uint32_t len = be32(pos);
+        if (pos + 12 + (size_t)len > buf.size()) return fail("truncated chunk");
+        const std::string type(reinterpret_cast<const char *>(&buf[pos + 4]), 4);
+        const uint8_t *d = &buf[pos + 8];
+        if (type == "IHDR") {
+            if (len < 13) return fail("bad IHDR");
+            w = be32(pos + 8);
+            h = be32(pos + 12);
+            depth = d[8];
+            ctype = d[9];
+            if (d[12] != 0) return fail("interlaced PNG not supported");
+        } else if (type == "IDAT") {
+            idat.insert(idat.end(), d, d + len);
+        } else if (type == "IEND") {
+            break;
+        }
+        pos += 12 + (size_t)len;
+    }
+    const int cn = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 4 ? 2 : ctype == 6 ? 4 : 0;
+    if (!w || !h || !cn || (depth != 8 && depth != 16)) return fail("unsupported PNG (need 8/16-bit grey or RGB, no palette)");
+    const size_t bpp = (size_t)cn * depth / 8, stride = bpp * w;
+    std::vector<uint8_t> raw((stride + 1) * h);
+    uLongf raw_len = (uLongf)raw.size();
+    if (uncompress(raw.data(), &raw_len, idat.data(), (uLong)idat.size()) != Z_OK || raw_len != raw.size()) return fail("bad zlib stream");
+    std::vector<uint8_t> prev(stride, 0), cur(stride);
+    out = Map<uint16_t>((int)h, (int)w, cn);
+    for (uint32_t y = 0; y < h; ++y) {
+        const uint8_t *line = &raw[(stride + 1) * y];
+        const int filter = line[0];
+        for (size_t x = 0; x < stride; ++x) {
+            const int a = x >= bpp ? cur[x - bpp] : 0, b = prev[x], c = x >= bpp ? prev[x - bpp] : 0;
+            int pred = 0;
+            if (filter == 1) pred = a;
+            else if (filter == 2) pred = b;
+            else if (filter == 3) pred = (a + b) >> 1;
+            else if (filter == 4) {
+                const int pp = a + b - c, pa = abs(pp - a), pb = abs(pp - b), pc = abs(pp - c);
+                pred = (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+            } else if (filter != 0) return fail("bad filter type");
+            cur[x] = (uint8_t)(line[1 + x] + pred);
+        }
+        for (uint32_t x = 0; x < w; ++x)
+            for (int k = 0; k < cn; ++k) {
+                const int src = (cn >= 3 && k < 3) ? 2 - k : k;   // RGB(A) in the file -> BGR(A) like cv::imread
+                const uint8_t *sp = &cur[(size_t)x * bpp + (size_t)src * depth / 8];
+                out.data[((size_t)y * w + x) * cn + k] = depth == 16 ? (uint16_t)((sp[0] << 8) | sp[1]) : sp[0];
+            }
+        prev.swap(cur);
+    }
+    if (bit_depth) *bit_depth = depth;
+    return true;
+}
+#endif
 
 // Images.  OpenCV's codecs are not available to C++ in this build: binary PGM / PPM (P5 / P6,
 // maxval 255) and the raw container the parity harness uses ("ACMRAW1 rows cols channels\n" +

@@ -64,6 +64,7 @@ EXPORTS = [
     "acmmp_fusion_set_view_second", "acmmp_fusion_run_prior_aware",
     "acmmp_jpeg_info", "acmmp_decode_jpeg", "acmmp_jpeg_last_error",
     "acmmp_pair_scores", "acmmp_pairs_last_error",
+    "acmmp_scan_set_prior_maps", "acmmp_prior_planes_from_maps", "acmmp_seeded_last_error",
     "acmmp_scan_create", "acmmp_scan_destroy", "acmmp_scan_last_error", "acmmp_scan_set_image",
     "acmmp_scan_set_shard", "acmmp_scan_set_sequential_geom", "acmmp_scan_num_levels", "acmmp_scan_begin_level",
     "acmmp_scan_run_stage", "acmmp_scan_exchange", "acmmp_scan_view_size", "acmmp_scan_get_view", "acmmp_scan_view_device",
@@ -168,6 +169,10 @@ def load():
     lib.acmmp_pair_scores.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.c_int64, dp, dp,
                                       C.c_double, C.c_double, dp, dp]
     lib.acmmp_pairs_last_error.restype = C.c_char_p
+    u16p = C.POINTER(C.c_uint16)
+    lib.acmmp_scan_set_prior_maps.argtypes = [vp, C.c_int, u16p, u16p, C.c_int, C.c_int]
+    lib.acmmp_prior_planes_from_maps.argtypes = [C.c_int, C.POINTER(Camera), u16p, u16p, C.c_int, C.c_int, C.c_int, C.c_int, fp]
+    lib.acmmp_seeded_last_error.restype = C.c_char_p
     lib.acmmp_scan_view_device.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     lib.acmmp_scan_count_ncc.argtypes = [vp, C.c_int]
     lib.acmmp_scan_ncc_count.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]

@@ -3,6 +3,9 @@
 // runs the multi-scale schedule (photometric + planar prior, geom x2 per scale) resident on
 // the device, writes <dense_folder><output_dir>/2333_%08d/{depths,depths_geom,normals,costs}.dmb
 // and fuses into ACMMP_model.ply.  Hand-rolled flag parser (Boost is not in this image).
+// -p / --prior: seeded mode - <dense_folder>/priors/{depths,normals}/%08d.png (16 bit) give the initial
+// hypotheses of the first scale (pSampler, acmmp_definitions.cpp:7-177); output goes to /ACMMP_PRIOR
+// unless --output_dir is given (main_ACMMP.cpp:79-85).
 // --force_fusion / --multi_fusion [DIR] / --single_match_penalty N select the prior-aware fusion
 // (main_ACMMP.cpp:178-189): map set 0 is read from <dense_folder><DIR>/2333_*/, set 1 is this run's.
 #include <sys/stat.h>
@@ -15,6 +18,7 @@
 #include <vector>
 
 #define ACMMP_IO_WITH_JPEG 1
+#define ACMMP_IO_WITH_PNG 1
 #include "../acmmp_b200/host/acmmp.hpp"
 
 using namespace acmmp_b200;
@@ -42,6 +46,7 @@ int main(int argc, char **argv) {
     unsigned long long seed = 0;
     bool fuse = true, force_fusion = false, multi_fusion = false, prior = false;
     std::string fusion_dir = "/ACMMP";
+    bool renamed_outdir = false;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto value = [&](const char *name) -> const char * {
@@ -57,7 +62,10 @@ int main(int argc, char **argv) {
                    "                  [--force_fusion] [--multi_fusion [/DIR]] [--single_match_penalty N] [-p|--prior]\n");
             return 1;
         } else if (a == "--dense_folder") dense_folder = value("--dense_folder");
-        else if (a == "--output_dir") output_dir = value("--output_dir");
+        else if (a == "--output_dir") {
+            output_dir = value("--output_dir");
+            renamed_outdir = true;
+        }
         else if (a == "-f" || a == "--fuse_thresh") consistency_scalar = (float)atof(value("--fuse_thresh"));
         else if (a == "--num_consistent_thresh") num_consistent_thresh = atoi(value("--num_consistent_thresh"));
         else if (a == "--mask_dir") mask_dir = value("--mask_dir");
@@ -117,11 +125,25 @@ int main(int argc, char **argv) {
                 pairs[i].push_back(it->second);
             }
         }
+        if (prior && !renamed_outdir) output_dir = "/ACMMP_PRIOR";   // main_ACMMP.cpp:79-85
         const std::string output_folder = dense_folder + output_dir;
         mkdir(output_folder.c_str(), 0777);
 
         Scan scan(cams, pairs, device);
         for (int i = 0; i < n; ++i) scan.SetImage(i, ToGrayFloat(images[i]));
+        if (prior) {
+            // the reference numbers the prior images by problem index, not by image id (acmmp_definitions.cpp:278, :104-105)
+            for (int i = 0; i < n; ++i) {
+                Map<uint16_t> d16, n16;
+                std::string err;
+                if (!ReadPng16(dense_folder + "/priors/depths/" + id_name(i, ".png"), d16, nullptr, &err) ||
+                    !ReadPng16(dense_folder + "/priors/normals/" + id_name(i, ".png"), n16, nullptr, &err)) {
+                    fprintf(stderr, "Initialisation from a prior was requested, but no suitable priors were found: %s\n", err.c_str());
+                    return -1;
+                }
+                scan.SetPriorMaps(i, d16, n16);
+            }
+        }
         std::vector<Map<float>> photo_depth(n);
         const int levels = scan.NumLevels();
         for (int level = 0; level < levels; ++level) {

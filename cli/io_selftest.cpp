@@ -1,17 +1,34 @@
 // io_selftest.cpp - exercises acmmp_b200/host/io.hpp from the CPU test-suite (tests/test_host_io.py):
 //   io_selftest <dir>   reads <dir>/pair.txt, <dir>/cams/00000000_cam.txt, <dir>/in.dmb, <dir>/img.ppm, <dir>/points.bin
+//   io_selftest --png in.png out.bin   decodes a PNG (ReadPng16) and dumps the samples
 //                       writes <dir>/out.dmb, <dir>/gray.dmb, <dir>/out.ply and prints what it parsed as key=value lines
 #include <cstdio>
 #include <cstdlib>
 #include <string>
 #include <vector>
 
+#define ACMMP_IO_WITH_PNG 1
 #include "../acmmp_b200/host/io.hpp"
 
 using namespace acmmp_b200;
 
 int main(int argc, char **argv) {
     if (argc < 2) return 2;
+    if (argc >= 4 && std::string(argv[1]) == "--png") {   // io_selftest --png in.png out.bin: raw samples (u16, cv::imread(-1) order)
+        Map<uint16_t> png;
+        int depth = 0;
+        std::string perr;
+        if (!ReadPng16(argv[2], png, &depth, &perr)) {
+            fprintf(stderr, "%s\n", perr.c_str());
+            return 12;
+        }
+        printf("png=%d,%d,%d,%d\n", png.rows, png.cols, png.channels, depth);
+        FILE *o = fopen(argv[3], "wb");
+        if (!o) return 13;
+        fwrite(png.data.data(), sizeof(uint16_t), png.data.size(), o);
+        fclose(o);
+        return 0;
+    }
     const std::string dir = argv[1];
     std::vector<Problem> problems;
     if (!GenerateSampleList(dir, problems)) return 3;

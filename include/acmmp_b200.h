@@ -303,6 +303,21 @@ int acmmp_scan_view_size(const acmmp_scan *s, int view, int *w, int *h);
 /* current maps of an owned view (.dmb payloads; depth = the last written depth
  * map); host pointers, any may be NULL. */
 int acmmp_scan_get_view(acmmp_scan *s, int view, float *depth, float *normal3, float *cost);
+/* Seeded mode (the reference's `-p`: pSampler, /root/reference/src/acmmp_definitions.cpp:7-177,
+ * ProcessProblem :274-280, main_ACMMP.cpp:107-121).  Hands over the 16-bit prior images of a view
+ * (what cv::imread(path, -1) returns for <dense>priors/depths/%08d.png and .../normals/%08d.png:
+ * prior_rows x prior_cols, the normal image's three channels in stored order, channel 0 = x).  The
+ * photometric stage of the FIRST scale then starts from these planes instead of random ones.
+ * Both pointers NULL: back to the unseeded schedule for this view.  Call before acmmp_scan_run_stage. */
+int acmmp_scan_set_prior_maps(acmmp_scan *s, int view, const uint16_t *depth16, const uint16_t *normal16x3,
+                              int prior_rows, int prior_cols);
+/* The conversion on its own (pSampler::GetPriorPlaneEstimate): planes4 = rows x cols x (nx, ny, nz in
+ * the camera frame, distance to the origin); cam = the view's camera at rows x cols. */
+int acmmp_prior_planes_from_maps(int device, const acmmp_camera *cam, const uint16_t *depth16,
+                                 const uint16_t *normal16x3, int prior_rows, int prior_cols, int rows, int cols,
+                                 float *planes4);
+const char *acmmp_seeded_last_error(void);
+
 /* the same maps as device pointers (valid until the next stage / level of the scan), e.g. to
  * hand them to acmmp_fusion_set_view(..., on_device = 1) after acmmp_scan_sync */
 int acmmp_scan_view_device(acmmp_scan *s, int view, const float **d_depth, const float **d_normal3, const float **d_cost);

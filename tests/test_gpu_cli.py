@@ -164,3 +164,46 @@ def test_cli_prior_aware_fusion_against_reference(cli_run):
         same = (ref_xyz_n.view(np.uint32) == xyz_n.view(np.uint32)).all(1).mean()
         assert same >= 0.999, same
         assert (ref_col == col).all()
+
+
+def test_cli_seeded_mode_reads_prior_pngs(cli_run):
+    """-p: <dense>/priors/{depths,normals}/%08d.png (16-bit PNG, numbered by problem index) seed the first
+    scale; the maps written under /ACMMP_PRIOR equal a scan seeded through the Python host with the arrays
+    cv2.imread(path, -1) returns."""
+    cv2 = pytest.importorskip("cv2")
+    from acmmp_b200 import host
+    from seeded_inputs import encode_priors
+    sc, dense, ids, _ = cli_run
+    n = len(ids)
+    priors = []
+    for v in range(n):
+        nrm = np.zeros(sc["depths"][v].shape + (3,))
+        nrm[..., 2] = -1.0
+        nrm[..., 0] = 0.1
+        d16, n16 = encode_priors(sc["cams"][v], sc["depths"][v], nrm, noise=0.01, seed=v)
+        os.makedirs(os.path.join(dense, "priors", "depths"), exist_ok=True)
+        os.makedirs(os.path.join(dense, "priors", "normals"), exist_ok=True)
+        assert cv2.imwrite(os.path.join(dense, "priors", "depths", "%08d.png" % v), d16)
+        assert cv2.imwrite(os.path.join(dense, "priors", "normals", "%08d.png" % v), n16)   # cv2 stores channel 0 as blue
+        back = cv2.imread(os.path.join(dense, "priors", "normals", "%08d.png" % v), -1)
+        assert (back == n16).all()
+        priors.append((d16, n16))
+    out = subprocess.run([EXE, dense, "-p", "--seed", "5", "--no_fusion"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    s = host.Scan(sc["cams"], sc["pairs"])
+    for v in range(n):
+        s.set_image(v, np.clip(np.rint(sc["images"][v]), 0, 255).astype(np.float32))
+        s.set_prior_maps(v, *priors[v])
+    s.run_all(seed=5)
+    s.sync()
+    for v in range(n):
+        depth, normal, cost = s.get_view(v)
+        folder = os.path.join(dense, "ACMMP_PRIOR", "2333_%08d" % ids[v])
+        assert (read_dmb(os.path.join(folder, "depths_geom.dmb")).view(np.uint32) == depth.view(np.uint32)).all()
+        assert (read_dmb(os.path.join(folder, "normals.dmb")).view(np.uint32) == normal.view(np.uint32)).all()
+    s.close()
+    # without the prior images the mode refuses to start, as the reference does (main_ACMMP.cpp:73-77)
+    import shutil as sh
+    sh.rmtree(os.path.join(dense, "priors"))
+    out = subprocess.run([EXE, dense, "-p", "--no_fusion"], capture_output=True, text=True)
+    assert out.returncode != 0 and "no suitable priors" in out.stderr

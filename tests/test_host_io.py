@@ -63,3 +63,37 @@ def test_formats_round_trip(tmp_path):
     exp[3, :3] = 0                                                     # non-finite coordinates are zeroed (ACMMP.cpp:414-418)
     assert np.array_equal(rec["f"], exp[:, :6])
     assert np.array_equal(rec["c"], exp[:, [8, 7, 6]].astype(np.uint8))  # red, green, blue = c2, c1, c0
+
+
+def test_png_reader_against_cv2(tmp_path):
+    """ReadPng16 (acmmp_b200/host/io.hpp; zlib) returns what cv2.imread(path, -1) returns: 8/16-bit,
+    grey / RGB / RGBA, every filter type the encoder picks - the 16-bit prior images of the seeded mode."""
+    cv2 = pytest.importorskip("cv2")
+    exe = os.path.join(ROOT, "build", "io_selftest")
+    if not os.path.exists(exe):
+        pytest.skip("build/io_selftest not built (make cli)")
+    rng = np.random.default_rng(3)
+    ramp = (np.add.outer(np.arange(37), np.arange(53)) * 400).astype(np.uint16)           # smooth: sub / up / paeth filters
+    cases = {
+        "g16": rng.integers(0, 65536, (37, 53)).astype(np.uint16),
+        "ramp16": ramp,
+        "c16": np.stack([ramp, ramp[::-1], rng.integers(0, 65536, (37, 53)).astype(np.uint16)], -1),
+        "g8": rng.integers(0, 256, (20, 31)).astype(np.uint8),
+        "c8": (np.stack([ramp, ramp.T[:37, :53] if False else ramp // 3, ramp // 7], -1) >> 8).astype(np.uint8),
+        "a16": rng.integers(0, 65536, (9, 11, 4)).astype(np.uint16),
+    }
+    for name, img in cases.items():
+        path = str(tmp_path / (name + ".png"))
+        assert cv2.imwrite(path, img)
+        back = cv2.imread(path, -1)
+        assert (back == img).all()
+        out = str(tmp_path / (name + ".bin"))
+        r = subprocess.run([exe, "--png", path, out], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        rows, cols, cn, depth = [int(x) for x in r.stdout.strip().split("=")[1].split(",")]
+        assert (rows, cols) == img.shape[:2] and cn == (1 if img.ndim == 2 else img.shape[2]) and depth == 8 * img.dtype.itemsize
+        mine = np.fromfile(out, np.uint16).reshape(img.shape)
+        assert (mine == img).all(), name
+    bad = str(tmp_path / "bad.png")
+    open(bad, "wb").write(b"not a png")
+    assert subprocess.run([exe, "--png", bad, str(tmp_path / "x.bin")], capture_output=True).returncode == 12
