@@ -72,6 +72,7 @@ struct LayeredImages {
     cudaArray_t arr = nullptr;
     cudaTextureObject_t tex = 0;
     int w = 0, h = 0, layers = 0;
+    bool u8 = false;   // R8 unorm texels (integer grey levels, read as normalised float) instead of R32F
 };
 
 }  // namespace
@@ -93,6 +94,11 @@ struct acmmp_ctx {
     int W = 0, H = 0;
     std::vector<acmmp_camera> cams;
     LayeredImages views;
+    // ACMMP_TEX_R32F: always float texels.  ACMMP_TEX_AUTO: R8 unorm texels when every image of the
+    // problem holds integer grey levels 0..255 (bit-identical results, ncc.cuh), else float texels
+    int tex_format = ACMMP_TEX_R32F;
+    bool ext_tex_u8 = false;
+    DevBuf stage_u8, u8_flag;
     // resident path: all views of a scan live in one layered array owned by the scan;
     // a problem then only names layers (no per-problem upload)
     cudaTextureObject_t ext_tex = 0;
@@ -159,9 +165,51 @@ void destroy_views(LayeredImages &v) {
 // layered float array + texture object with the reference's sampling state
 // (ACMMP.cpp:646-663): linear filter, unnormalised coordinates, "wrap" (not
 // honoured for unnormalised coordinates: the hardware clamps).
-int ensure_views(acmmp_ctx *ctx, int w, int h, int layers) {
+cudaError_t make_layered(LayeredImages &v, int w, int h, int layers, bool u8) {
+    destroy_views(v);
+    cudaChannelFormatDesc desc = u8 ? cudaCreateChannelDesc(8, 0, 0, 0, cudaChannelFormatKindUnsigned)
+                                    : cudaCreateChannelDesc(32, 0, 0, 0, cudaChannelFormatKindFloat);
+    cudaError_t e = cudaMalloc3DArray(&v.arr, &desc, make_cudaExtent(w, h, layers), cudaArrayLayered);
+    if (e != cudaSuccess) return e;
+    cudaResourceDesc res;
+    memset(&res, 0, sizeof res);
+    res.resType = cudaResourceTypeArray;
+    res.res.array.array = v.arr;
+    cudaTextureDesc td;
+    memset(&td, 0, sizeof td);
+    td.addressMode[0] = cudaAddressModeWrap;   // as ACMMP.cpp:655-661; clamps for unnormalised coordinates
+    td.addressMode[1] = cudaAddressModeWrap;
+    td.filterMode = cudaFilterModeLinear;
+    td.readMode = u8 ? cudaReadModeNormalizedFloat : cudaReadModeElementType;
+    td.normalizedCoords = 0;
+    e = cudaCreateTextureObject(&v.tex, &res, &td, nullptr);
+    if (e != cudaSuccess) return e;
+    v.w = w;
+    v.h = h;
+    v.layers = layers;
+    v.u8 = u8;
+    return cudaSuccess;
+}
+
+// bytes of one layer -> layer `layer` of an R8 array
+cudaError_t copy_layer_u8(const LayeredImages &v, int layer, const uint8_t *d_src, cudaStream_t st) {
+    cudaMemcpy3DParms cp;
+    memset(&cp, 0, sizeof cp);
+    cp.srcPtr = make_cudaPitchedPtr(const_cast<uint8_t *>(d_src), (size_t)v.w, v.w, v.h);
+    cp.dstArray = v.arr;
+    cp.dstPos = make_cudaPos(0, 0, layer);
+    cp.extent = make_cudaExtent(v.w, v.h, 1);
+    cp.kind = cudaMemcpyDeviceToDevice;
+    return cudaMemcpy3DAsync(&cp, st);
+}
+
+int ensure_views(acmmp_ctx *ctx, int w, int h, int layers, bool u8 = false) {
     LayeredImages &v = ctx->views;
-    if (v.arr && v.w == w && v.h == h && v.layers >= layers) return 0;
+    if (v.arr && v.w == w && v.h == h && v.layers >= layers && v.u8 == u8) return 0;
+    if (u8) {
+        CU(ctx, make_layered(v, w, h, layers, true));
+        return 0;
+    }
     destroy_views(v);
     cudaChannelFormatDesc desc = cudaCreateChannelDesc(32, 0, 0, 0, cudaChannelFormatKindFloat);
     CU(ctx, cudaMalloc3DArray(&v.arr, &desc, make_cudaExtent(w, h, layers), cudaArrayLayered));
@@ -180,6 +228,51 @@ int ensure_views(acmmp_ctx *ctx, int w, int h, int layers) {
     v.w = w;
     v.h = h;
     v.layers = layers;
+    v.u8 = false;
+    return 0;
+}
+
+// ACMMP_TEX_AUTO: all views as bytes into an R8 array; *ok = 0 when some image does not hold
+// integer grey levels (the caller then uploads float texels)
+int upload_views_u8(acmmp_ctx *ctx, int n, const acmmp_camera *cams, const float *const *images, bool on_device, int maxw,
+                    int maxh, int *ok) {
+    *ok = 0;
+    CU(ctx, ctx->u8_flag.ensure(sizeof(int)));
+    CU(ctx, cudaMemsetAsync(ctx->u8_flag.p, 0, sizeof(int), ctx->stream));
+    // every image is checked before the array changes format (a float problem keeps its array)
+    std::vector<const float *> d_img(n);
+    size_t total = 0;
+    for (int i = 0; i < n; ++i) total += (size_t)cams[i].width * cams[i].height;
+    if (!on_device) {
+        CU(ctx, ctx->stage_in.ensure(total * sizeof(float)));
+        size_t off = 0;
+        for (int i = 0; i < n; ++i) {
+            const size_t P = (size_t)cams[i].width * cams[i].height;
+            CU(ctx, cudaMemcpyAsync(ctx->stage_in.as<float>() + off, images[i], P * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+            d_img[i] = ctx->stage_in.as<float>() + off;
+            off += P;
+        }
+    } else {
+        for (int i = 0; i < n; ++i) d_img[i] = images[i];
+    }
+    for (int i = 0; i < n; ++i) {
+        CU(ctx, launch_check_u8(d_img[i], (size_t)cams[i].width * cams[i].height, ctx->u8_flag.as<int>(), ctx->stream));
+        ctx->launches++;
+    }
+    int bad = 0;
+    CU(ctx, cudaMemcpyAsync(&bad, ctx->u8_flag.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    if (bad) return 0;
+    int rcode = ensure_views(ctx, maxw, maxh, n, true);
+    if (rcode) return rcode;
+    CU(ctx, ctx->stage_u8.ensure((size_t)maxw * maxh * n));
+    for (int i = 0; i < n; ++i) {
+        uint8_t *dst = ctx->stage_u8.as<uint8_t>() + (size_t)i * maxw * maxh;
+        CU(ctx, launch_to_u8_replicate(d_img[i], cams[i].width, cams[i].height, dst, maxw, maxh, ctx->stream));
+        ctx->launches++;
+        CU(ctx, copy_layer_u8(ctx->views, i, dst, ctx->stream));
+    }
+    *ok = 1;
     return 0;
 }
 
@@ -262,13 +355,14 @@ int problem_common(acmmp_ctx *ctx, int n, const acmmp_camera *cams) {
 
 // resident path: the views already sit in layers of `tex` (owned by the caller);
 // ref_image = row-major reference image on the device (borrowed)
-int set_problem_resident(acmmp_ctx *ctx, int n, const acmmp_camera *cams, cudaTextureObject_t tex, const float *ref_image,
-                         const int *layers) {
+int set_problem_resident(acmmp_ctx *ctx, int n, const acmmp_camera *cams, cudaTextureObject_t tex, bool tex_u8,
+                         const float *ref_image, const int *layers) {
     if (n < 2 || n - 1 > ACMMP_MAX_SRC_VIEWS) return fail(ctx, ACMMP_ERR_INVALID, "need 1 reference + 1..%d source views, got n=%d", ACMMP_MAX_SRC_VIEWS, n);
     if (bind_device(ctx)) return ACMMP_ERR_CUDA;
     ctx->n = n;
     ctx->cams.assign(cams, cams + n);
     ctx->ext_tex = tex;
+    ctx->ext_tex_u8 = tex_u8;
     ctx->ext_ref_image = ref_image;
     ctx->layers.assign(layers, layers + n);
     return problem_common(ctx, n, cams);
@@ -330,6 +424,7 @@ int create_sibling(acmmp_ctx **out, const acmmp_ctx *first) {
     ctx->owns_stream = false;
     acmmp_default_params(&ctx->params);
     ctx->compat = first->compat;
+    ctx->tex_format = first->tex_format;
     *out = ctx;
     return 0;
 }
@@ -346,7 +441,7 @@ void acmmp_destroy(acmmp_ctx *ctx) {
     DevBuf *bufs[] = {&ctx->ref_image, &ctx->d_cams, &ctx->stage_in, &ctx->stage_pad, &ctx->d_depth_ptrs, &ctx->d_rc, &ctx->d_pairs,
                       &ctx->planes, &ctx->costs, &ctx->pre_costs, &ctx->sel, &ctx->rng, &ctx->planes_snap,
                       &ctx->costs_snap, &ctx->seeded, &ctx->prior_planes, &ctx->plane_masks, &ctx->scaled_planes,
-                      &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c, &ctx->tri_buf, &ctx->ncc_counter};
+                      &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c, &ctx->tri_buf, &ctx->ncc_counter, &ctx->stage_u8, &ctx->u8_flag};
     for (auto *b : bufs) b->release();
     for (auto &ev : ctx->evpool)
         if (ev) cudaEventDestroy(ev);
@@ -383,6 +478,17 @@ int acmmp_set_compat_mode(acmmp_ctx *ctx, int mode) {
     ctx->compat = mode;
     return 0;
 }
+int acmmp_set_texture_format(acmmp_ctx *ctx, int format) {
+    if (!ctx) return ACMMP_ERR_INVALID;
+    if (format != ACMMP_TEX_R32F && format != ACMMP_TEX_AUTO)
+        return fail(ctx, ACMMP_ERR_INVALID, "unknown texture format %d", format);
+    ctx->tex_format = format;
+    return 0;
+}
+int acmmp_texture_is_u8(const acmmp_ctx *ctx) {
+    if (!ctx) return 0;
+    return ctx->ext_tex ? (ctx->ext_tex_u8 ? 1 : 0) : (ctx->views.u8 ? 1 : 0);
+}
 int acmmp_get_params(const acmmp_ctx *ctx, acmmp_params *out) {
     if (!ctx || !out) return ACMMP_ERR_INVALID;
     *out = ctx->params;
@@ -416,15 +522,21 @@ int acmmp_set_problem(acmmp_ctx *ctx, int n, const acmmp_camera *cams, const flo
         if (cams[i].width > maxw) maxw = cams[i].width;
         if (cams[i].height > maxh) maxh = cams[i].height;
     }
-    {
+    int as_u8 = 0;
+    if (ctx->tex_format == ACMMP_TEX_AUTO) {
+        int rcode = upload_views_u8(ctx, n, cams, images, images_on_device != 0, maxw, maxh, &as_u8);
+        if (rcode) return rcode;
+    }
+    if (!as_u8) {
         int rcode = ensure_views(ctx, maxw, maxh, n);
         if (rcode) return rcode;
-    }
-    for (int i = 0; i < n; ++i) {
-        int rcode = upload_layer(ctx, i, images[i], cams[i].width, cams[i].height, images_on_device != 0);
-        if (rcode) return rcode;
+        for (int i = 0; i < n; ++i) {
+            rcode = upload_layer(ctx, i, images[i], cams[i].width, cams[i].height, images_on_device != 0);
+            if (rcode) return rcode;
+        }
     }
     ctx->ext_tex = 0;
+    ctx->ext_tex_u8 = false;
     ctx->ext_ref_image = nullptr;
     ctx->layers.resize(n);
     for (int i = 0; i < n; ++i) ctx->layers[i] = i;

@@ -344,11 +344,13 @@ cudaError_t launch_init(const InitLaunch &L, cudaStream_t st) {
     const size_t smem = init_smem_bytes(L.nsrc);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(init_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(init_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(init_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    init_kernel<<<grid2(L.W, L.H, kInitTileW, kInitTileH), kInitThreads, smem, st>>>(a);
+    if (L.tex_u8) init_kernel<true><<<grid2(L.W, L.H, kInitTileW, kInitTileH), kInitThreads, smem, st>>>(a);
+    else init_kernel<false><<<grid2(L.W, L.H, kInitTileW, kInitTileH), kInitThreads, smem, st>>>(a);
     return cudaGetLastError();
 }
 
@@ -366,11 +368,13 @@ cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st) {
     const size_t smem = sweep_smem_bytes(L.nsrc);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(sweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(sweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    sweep_kernel<<<grid2(L.W, L.H, kTileW, kTileH), kSweepThreads, smem, st>>>(a);
+    if (L.tex_u8) sweep_kernel<true><<<grid2(L.W, L.H, kTileW, kTileH), kSweepThreads, smem, st>>>(a);
+    else sweep_kernel<false><<<grid2(L.W, L.H, kTileW, kTileH), kSweepThreads, smem, st>>>(a);
     return cudaGetLastError();
 }
 
@@ -411,10 +415,37 @@ cudaError_t launch_pad_replicate(const float *src, int w, int h, float *dst, int
     return cudaGetLastError();
 }
 
+// integer grey levels?  (decoded 8-bit images that were never resized)
+__global__ void check_u8_kernel(const float *__restrict__ src, size_t n, int *not_u8) {
+    bool bad = false;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float v = src[i];
+        bad |= !(v >= 0.0f && v <= 255.0f && v == truncf(v));
+    }
+    if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(not_u8, 1);
+}
+cudaError_t launch_check_u8(const float *src, size_t n, int *not_u8, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    size_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    check_u8_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, n, not_u8);
+    return cudaGetLastError();
+}
+__global__ void to_u8_replicate_kernel(const float *__restrict__ src, int w, int h, uint8_t *__restrict__ dst, int W, int H) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= W || y >= H) return;
+    dst[(size_t)y * W + x] = (uint8_t)__float2int_rn(src[(size_t)min(y, h - 1) * w + min(x, w - 1)]);
+}
+cudaError_t launch_to_u8_replicate(const float *src, int w, int h, uint8_t *dst, int W, int H, cudaStream_t st) {
+    to_u8_replicate_kernel<<<grid2(W, H, 32, 8), dim3(32, 8), 0, st>>>(src, w, h, dst, W, H);
+    return cudaGetLastError();
+}
+
 // bilinear fetch rate of a layered R32F texture.  mode 0: a warp reads 32 horizontally
 // adjacent pixels (best case); mode 1: the sweep kernel's shape - 8 lanes around each of
 // 4 pixels, a few pixels apart, taps advancing by 2 pixels.
-__global__ void tex_peak_kernel(cudaTextureObject_t tex, int w, int h, int layers, int iters, int mode, float *out) {
+// u8: R8 unorm texels + the two-operation rounding of bilateral_ncc<true>.
+__global__ void tex_peak_kernel(cudaTextureObject_t tex, int u8, int w, int h, int layers, int iters, int mode, float *out) {
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = tid >> 5;
     float bx, by;
@@ -430,25 +461,31 @@ __global__ void tex_peak_kernel(cudaTextureObject_t tex, int w, int h, int layer
     for (int i = 0; i < iters; ++i) {
         const float x = bx + (float)(2 * (i % 6));
         const float y = by + (float)(2 * ((i / 6) % 6)) + (float)(i / 36);
-        acc += tex2DLayered<float>(tex, x, y, layer);
+        float t = tex2DLayered<float>(tex, x, y, layer);
+        if (u8) t = fadd(ffma(t, 255.0f, 49152.0f), -49152.0f);
+        acc += t;
     }
     if (acc == 123.456f) out[tid] = acc;   // keeps the loop alive
 }
-cudaError_t launch_tex_peak(cudaTextureObject_t tex, int w, int h, int layers, int blocks, int threads, int iters, int mode,
+cudaError_t launch_tex_peak(cudaTextureObject_t tex, int u8, int w, int h, int layers, int blocks, int threads, int iters, int mode,
                             float *scratch, cudaStream_t st) {
-    tex_peak_kernel<<<blocks, threads, 0, st>>>(tex, w, h, layers, iters, mode, scratch);
+    tex_peak_kernel<<<blocks, threads, 0, st>>>(tex, u8, w, h, layers, iters, mode, scratch);
     return cudaGetLastError();
 }
 
 // one bilinear fetch per coordinate, through the same texture set-up as the problem's views
-__global__ void tex_sample_kernel(cudaTextureObject_t tex, const float *__restrict__ xs, const float *__restrict__ ys, int n,
+// (u8: the same rounding back onto the 1/256 grid as bilateral_ncc<true>, ncc.cuh)
+__global__ void tex_sample_kernel(cudaTextureObject_t tex, int u8, const float *__restrict__ xs, const float *__restrict__ ys, int n,
                                   float *__restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = tex2DLayered<float>(tex, xs[i], ys[i], 0);
+    if (i >= n) return;
+    float s = tex2DLayered<float>(tex, xs[i], ys[i], 0);
+    if (u8) s = fadd(ffma(s, 255.0f, 49152.0f), -49152.0f);
+    out[i] = s;
 }
-cudaError_t launch_tex_sample(cudaTextureObject_t tex, const float *xs, const float *ys, int n, float *out, cudaStream_t st) {
+cudaError_t launch_tex_sample(cudaTextureObject_t tex, int u8, const float *xs, const float *ys, int n, float *out, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
-    tex_sample_kernel<<<(n + 255) / 256, 256, 0, st>>>(tex, xs, ys, n, out);
+    tex_sample_kernel<<<(n + 255) / 256, 256, 0, st>>>(tex, u8, xs, ys, n, out);
     return cudaGetLastError();
 }
 

@@ -22,6 +22,7 @@ struct InitLaunch {
     uint32_t *rng6;
     const float *ref_image;
     cudaTextureObject_t tex;
+    int tex_u8;   // tex is an R8 unorm array of integer grey levels (ncc.cuh), else R32F
     const PairConst *pairs;
     const RefConst *rc;
     int W, H, nsrc, mode, hierarchy, top_k;
@@ -40,6 +41,7 @@ struct SweepLaunch {
     uint32_t *rng6;
     const float *ref_image;
     cudaTextureObject_t tex;
+    int tex_u8;
     const PairConst *pairs;
     const RefConst *rc;
     int W, H, nsrc, iter, color;
@@ -63,12 +65,16 @@ cudaError_t launch_jbu_depth(const float *image, int w, int h, const float *sdep
                              float *out, cudaStream_t st);
 cudaError_t launch_resize_linear(const float *src, int sw, int sh, float *dst, int dw, int dh, cudaStream_t st);
 cudaError_t launch_pad_replicate(const float *src, int w, int h, float *dst, int W, int H, cudaStream_t st);
+// *not_u8 |= 1 when a pixel of src is not an integer grey level 0..255
+cudaError_t launch_check_u8(const float *src, size_t n, int *not_u8, cudaStream_t st);
+// float grey levels -> bytes, edges replicated up to W x H (the layer size)
+cudaError_t launch_to_u8_replicate(const float *src, int w, int h, uint8_t *dst, int W, int H, cudaStream_t st);
 cudaError_t launch_fp32_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
 // seeded.cu (IEEE build): seeded hypotheses of one view at the current level from its 16-bit prior images
 cudaError_t launch_prior_maps_to_planes(const acmmp_camera &cam, const uint16_t *depth16, const uint16_t *normal16, int prows,
                                         int pcols, int rows, int cols, float4 *planes, cudaStream_t st);
-cudaError_t launch_tex_sample(cudaTextureObject_t tex, const float *xs, const float *ys, int n, float *out, cudaStream_t st);
-cudaError_t launch_tex_peak(cudaTextureObject_t tex, int w, int h, int layers, int blocks, int threads, int iters, int mode,
+cudaError_t launch_tex_sample(cudaTextureObject_t tex, int u8, const float *xs, const float *ys, int n, float *out, cudaStream_t st);
+cudaError_t launch_tex_peak(cudaTextureObject_t tex, int u8, int w, int h, int layers, int blocks, int threads, int iters, int mode,
                             float *scratch, cudaStream_t st);
 cudaError_t launch_mufu_peak(float *scratch, int blocks, int threads, int iters, cudaStream_t st);
 cudaError_t launch_support_cells(const float *costs, int W, int H, int2 *cells, cudaStream_t st);

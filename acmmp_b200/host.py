@@ -54,6 +54,14 @@ class ACMMP:
     def SetCompatMode(self, mode):
         _check(self._ctx, self._lib.acmmp_set_compat_mode(self._ctx, int(mode)), "SetCompatMode")
 
+    def SetTextureFormat(self, fmt):
+        """L.TEX_R32F (default) or L.TEX_AUTO: R8 texels for the next problems whose images all hold
+        integer grey levels (bit-identical samples, a quarter of the texture footprint)."""
+        _check(self._ctx, self._lib.acmmp_set_texture_format(self._ctx, int(fmt)), "SetTextureFormat")
+
+    def TextureIsU8(self):
+        return bool(self._lib.acmmp_texture_is_u8(self._ctx))
+
     # ---- inputs ---------------------------------------------------------------------
     def InputInitialization(self, images, cams, depths=None):
         """images[0] / cams[0]: reference view (float32 HxW at this scale); the
@@ -243,6 +251,17 @@ def tex_sample(image, xs, ys, device=0):
     return out
 
 
+def tex_sample_u8(image, xs, ys, device=0):
+    """The same through an R8 unorm texture and the rounding of the kU8 kernels (ncc.cuh); `image` must hold
+    integer grey levels 0..255."""
+    lib = L.load()
+    img, x, y = L.f32(image), L.f32(xs).ravel(), L.f32(ys).ravel()
+    out = np.empty(len(x), np.float32)
+    _check(None, lib.acmmp_tex_sample_u8(device, L.fptr(img), img.shape[1], img.shape[0], L.fptr(x), L.fptr(y), len(x), L.fptr(out)),
+           "tex_sample_u8")
+    return out
+
+
 def DelaunayTriangulation(points):
     """points (n,2) int -> triangles (m,3,2) int (ACMMP.cpp:896-918); host only."""
     lib = L.load()
@@ -270,11 +289,13 @@ def measure_fp32_peak(device=0):
     return a.value, b.value
 
 
-def measure_tex_peak(device=0):
-    """(coherent, grouped) bilinear fetch rate in G fetches/s: the propagation kernel's roofline."""
+def measure_tex_peak(device=0, u8=False):
+    """(coherent, grouped) bilinear fetch rate in G fetches/s: the propagation kernel's roofline
+    (u8: on R8 unorm texels incl. the rounding of the kU8 kernels)."""
     lib = L.load()
     a, b = C.c_double(), C.c_double()
-    _check(None, lib.acmmp_measure_tex_peak(device, C.byref(a), C.byref(b)), "measure_tex_peak")
+    fn = lib.acmmp_measure_tex_peak_u8 if u8 else lib.acmmp_measure_tex_peak
+    _check(None, fn(device, C.byref(a), C.byref(b)), "measure_tex_peak")
     return a.value, b.value
 
 
@@ -287,7 +308,7 @@ class Scan:
     stage with (device pointer, floats per rank segment) so that a multi-GPU caller
     can all-gather the depth maps (no-op on one GPU)."""
 
-    def __init__(self, cams, pairs, device=0, rank=0, world=1, sequential_geom=False):
+    def __init__(self, cams, pairs, device=0, rank=0, world=1, sequential_geom=False, tex_format=None):
         self._lib = L.load()
         self._s = C.c_void_p()
         n = len(cams)
@@ -303,6 +324,8 @@ class Scan:
         self.n, self.rank, self.world = n, rank, world
         self._ck(self._lib.acmmp_scan_set_shard(self._s, rank, world), "set_shard")
         self._ck(self._lib.acmmp_scan_set_sequential_geom(self._s, int(sequential_geom)), "set_sequential_geom")
+        if tex_format is not None:   # default of the library: L.TEX_AUTO
+            self._ck(self._lib.acmmp_scan_set_texture_format(self._s, int(tex_format)), "set_texture_format")
 
     def _ck(self, rc, what):
         if rc != 0:
@@ -338,6 +361,10 @@ class Scan:
 
     def begin_level(self, level):
         self._ck(self._lib.acmmp_scan_begin_level(self._s, level), "begin_level")
+
+    def level_is_u8(self):
+        """True when the current level's views sit in R8 texels (no resize, integer grey levels)."""
+        return bool(self._lib.acmmp_scan_level_is_u8(self._s))
 
     def run_stage(self, stage, seed=0):
         self._ck(self._lib.acmmp_scan_run_stage(self._s, stage, int(seed)), "run_stage")
@@ -423,9 +450,9 @@ class Scan:
         self._ck(self._lib.acmmp_scan_elapsed(self._s, i, j, C.byref(ms)), "elapsed")
         return float(ms.value)
 
-    def run_all(self, seed=0, exchange=None, stages=(STAGE_PHOTO, STAGE_GEOM0, STAGE_GEOM1), levels=None):
+    def run_all(self, seed=0, exchange=None, stages=(STAGE_PHOTO, STAGE_GEOM0, STAGE_GEOM1), levels=None, level_done=None):
         """the full-ACMMP schedule: for every level, coarse to fine: photometric +
-        planar prior, geom-0, geom-1."""
+        planar prior, geom-0, geom-1.  level_done(level): called after the last stage of a level."""
         nl = self.num_levels() if levels is None else levels
         for level in range(nl):
             self.begin_level(level)
@@ -433,6 +460,8 @@ class Scan:
                 self.run_stage(st, seed)
                 if exchange is not None:
                     exchange(*self.exchange_info())
+            if level_done is not None:
+                level_done(level)
 
 
 class Fusion:

@@ -10,6 +10,8 @@ LIB_PATH = os.environ.get("ACMMP_B200_LIB") or os.path.join(_HERE, "libacmmp_b20
 MAX_SRC_VIEWS = 32
 COMPAT_REF_SM100 = 0
 COMPAT_UPSTREAM = 1
+TEX_R32F = 0   # acmmp_tex_format
+TEX_AUTO = 1
 
 
 class Camera(C.Structure):
@@ -51,13 +53,13 @@ assert C.sizeof(Camera) == 100
 EXPORTS = [
     "acmmp_create", "acmmp_destroy", "acmmp_last_error", "acmmp_version", "acmmp_default_params",
     "acmmp_set_geom_consistency", "acmmp_set_hierarchy", "acmmp_set_planar_prior_params",
-    "acmmp_set_compat_mode", "acmmp_get_params", "acmmp_set_problem", "acmmp_set_depth_map",
+    "acmmp_set_compat_mode", "acmmp_set_texture_format", "acmmp_texture_is_u8", "acmmp_get_params", "acmmp_set_problem", "acmmp_set_depth_map",
     "acmmp_set_warm_start", "acmmp_set_hierarchy_inputs", "acmmp_set_seeded_planes",
     "acmmp_set_planar_prior", "acmmp_build_planar_prior", "acmmp_run", "acmmp_run_init",
     "acmmp_run_sweep", "acmmp_run_tail", "acmmp_get_result", "acmmp_get_maps",
     "acmmp_get_depth_device", "acmmp_get_state", "acmmp_set_state", "acmmp_width", "acmmp_height",
     "acmmp_sync", "acmmp_launch_count", "acmmp_last_timing", "acmmp_jbu_depth", "acmmp_resize_linear",
-    "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_measure_tex_peak", "acmmp_tex_sample", "acmmp_get_planar_prior", "acmmp_delaunay", "acmmp_timing_collect",
+    "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_measure_tex_peak", "acmmp_measure_tex_peak_u8", "acmmp_tex_sample", "acmmp_tex_sample_u8", "acmmp_get_planar_prior", "acmmp_delaunay", "acmmp_timing_collect",
     "acmmp_count_ncc", "acmmp_ncc_count", "acmmp_scan_count_ncc", "acmmp_scan_ncc_count",
     "acmmp_fusion_create", "acmmp_fusion_destroy", "acmmp_fusion_last_error", "acmmp_fusion_set_view", "acmmp_fusion_run",
     "acmmp_fusion_get_points", "acmmp_fusion_get_mask", "acmmp_fusion_stats",
@@ -66,7 +68,7 @@ EXPORTS = [
     "acmmp_pair_scores", "acmmp_pairs_last_error",
     "acmmp_scan_set_prior_maps", "acmmp_prior_planes_from_maps", "acmmp_seeded_last_error",
     "acmmp_scan_create", "acmmp_scan_destroy", "acmmp_scan_last_error", "acmmp_scan_set_image",
-    "acmmp_scan_set_shard", "acmmp_scan_set_sequential_geom", "acmmp_scan_num_levels", "acmmp_scan_begin_level",
+    "acmmp_scan_set_shard", "acmmp_scan_set_texture_format", "acmmp_scan_level_is_u8", "acmmp_scan_set_sequential_geom", "acmmp_scan_num_levels", "acmmp_scan_begin_level",
     "acmmp_scan_run_stage", "acmmp_scan_exchange", "acmmp_scan_view_size", "acmmp_scan_get_view", "acmmp_scan_view_device",
     "acmmp_scan_timing", "acmmp_scan_sync", "acmmp_scan_reset", "acmmp_scan_host_stats", "acmmp_scan_mark", "acmmp_scan_elapsed",
 ]
@@ -99,6 +101,8 @@ def load():
     lib.acmmp_set_hierarchy.argtypes = [vp]
     lib.acmmp_set_planar_prior_params.argtypes = [vp]
     lib.acmmp_set_compat_mode.argtypes = [vp, C.c_int]
+    lib.acmmp_set_texture_format.argtypes = [vp, C.c_int]
+    lib.acmmp_texture_is_u8.argtypes = [vp]
     lib.acmmp_get_params.argtypes = [vp, C.POINTER(Params)]
     lib.acmmp_set_problem.argtypes = [vp, C.c_int, C.POINTER(Camera), C.POINTER(vp), C.c_int]
     lib.acmmp_set_depth_map.argtypes = [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int]
@@ -130,7 +134,9 @@ def load():
     lib.acmmp_rng_init_states.argtypes = [C.c_int, C.c_uint64, C.c_int, C.c_int, up]
     lib.acmmp_measure_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.acmmp_measure_tex_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.acmmp_measure_tex_peak_u8.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.acmmp_tex_sample.argtypes = [C.c_int, fp, C.c_int, C.c_int, fp, fp, C.c_int, fp]
+    lib.acmmp_tex_sample_u8.argtypes = [C.c_int, fp, C.c_int, C.c_int, fp, fp, C.c_int, fp]
     i32p = C.POINTER(C.c_int32)
     lib.acmmp_scan_create.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.POINTER(Camera), i32p, i32p]
     lib.acmmp_scan_destroy.argtypes = [vp]
@@ -140,6 +146,8 @@ def load():
     lib.acmmp_scan_set_image.argtypes = [vp, C.c_int, vp, C.c_int]
     lib.acmmp_scan_set_shard.argtypes = [vp, C.c_int, C.c_int]
     lib.acmmp_scan_set_sequential_geom.argtypes = [vp, C.c_int]
+    lib.acmmp_scan_set_texture_format.argtypes = [vp, C.c_int]
+    lib.acmmp_scan_level_is_u8.argtypes = [vp]
     lib.acmmp_scan_num_levels.argtypes = [vp]
     lib.acmmp_scan_begin_level.argtypes = [vp, C.c_int]
     lib.acmmp_scan_run_stage.argtypes = [vp, C.c_int, C.c_uint64]

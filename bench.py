@@ -28,6 +28,8 @@ FLOP_PER_NCC = 1538.0          # 36 x 38 + 170
 # (ncu --set full, profiles/r1g_sweep_init_full_summary.txt: 311 MB read + 121 MB written, average of 8
 # launches); ~1 % of what HBM could move in that time
 SWEEP_DRAM_BYTES_PER_LAUNCH = 432e6
+# the same for sweep_kernel<R8> (finest level, R8 unorm texels); None until the ncu capture of this round is in profiles/
+SWEEP_DRAM_BYTES_PER_LAUNCH_U8 = None
 HYP_PER_RUN = 29               # 1 (init) + 2 x 14; 30 for the hierarchy (upsample-init) run
 
 
@@ -43,6 +45,8 @@ def parse_args():
     ap.add_argument("--nsrc", type=int, default=10)
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tex-format", default="auto", choices=["auto", "r32f"],
+                    help="auto: R8 unorm texels on levels that are not resized (bit-identical samples); r32f: float texels everywhere")
     ap.add_argument("--ref-views", type=int, default=4, help="views per step of the reference arm (bounded sample)")
     return ap.parse_args()
 
@@ -137,7 +141,9 @@ def run_ours(args):
         h_.copy_(d_)
     torch.cuda.synchronize()
     imgs_np = [t.numpy() for t in imgs_host]
-    scan = host.Scan(sc["cams"], sc["pairs"], device=local, rank=rank, world=world)
+    from acmmp_b200 import lib as L
+    scan = host.Scan(sc["cams"], sc["pairs"], device=local, rank=rank, world=world,
+                     tex_format=L.TEX_R32F if args.tex_format == "r32f" else L.TEX_AUTO)
     owned = scan.owned()
     H, W = args.height, args.width
     outs = {v: (torch.empty((H, W), dtype=torch.float32).pin_memory().numpy(),
@@ -155,6 +161,18 @@ def run_ours(args):
         torch.cuda.current_stream().synchronize()
         n_exchanges[0] += 1
 
+    # kernel time per pyramid level (CUDA events on the launching stream, collected after each level;
+    # the collection waits for the level's last kernel, which the next level's set-up does anyway)
+    level_tm = {}
+    level_u8 = {}
+
+    def level_done(level):
+        t = scan.timing()
+        acc = level_tm.setdefault(level, {"init_ms": 0.0, "sweeps_ms": 0.0, "tail_ms": 0.0, "total_ms": 0.0})
+        for k in acc:
+            acc[k] += t[k]
+        level_u8[level] = scan.level_is_u8()
+
     def step(e2e):
         scan.reset()
         for v in range(n):
@@ -162,7 +180,7 @@ def run_ours(args):
                 scan.set_image(v, imgs_np[v], sync=False)
             else:
                 scan.set_image(v, imgs_dev[v].data_ptr(), on_device=True)
-        scan.run_all(seed=1234, exchange=exchange)
+        scan.run_all(seed=1234, exchange=exchange, level_done=level_done)
         if e2e:
             for v in owned:
                 scan.get_view(v, out=outs[v])
@@ -190,10 +208,12 @@ def run_ours(args):
     barrier()
     scan.timing()                      # clear the kernel-time log
     l0 = scan.timing()["launches"]
+    level_tm.clear()
     with ClockSampler(local) as clocks:
         ms_dev = timed(args.steps, False)
-    tm = scan.timing()
-    launches = tm["launches"] - l0
+    launches = scan.timing()["launches"] - l0
+    level_tm_timed = {lv: dict(t) for lv, t in level_tm.items()}
+    tm = {k: sum(t[k] for t in level_tm_timed.values()) for k in ("init_ms", "sweeps_ms", "tail_ms", "total_ms")}
     step(True)                          # e2e warm-up (pinned staging paths)
     ms_e2e = timed(args.steps, True)
     sizes = []
@@ -206,13 +226,36 @@ def run_ours(args):
     scan.count_ncc(True)
     scan.ncc_count()
     ex0 = n_exchanges[0]
-    step(False)
+    ncc_level = {}
+
+    def count_level(level):
+        ncc_level[level] = scan.ncc_count()
+
+    scan.reset()
+    for v in range(n):
+        scan.set_image(v, imgs_dev[v].data_ptr(), on_device=True)
+    scan.run_all(seed=1234, exchange=exchange, level_done=count_level)
     scan.sync()
     exchanges_per_step = n_exchanges[0] - ex0
-    ncc = scan.ncc_count()
+    ncc = {k: sum(c[k] for c in ncc_level.values()) for k in ("init", "sweeps")}
     scan.count_ncc(False)
     fp32_tflops, mufu_gops = host.measure_fp32_peak(local)
     tex_coherent, tex_grouped = host.measure_tex_peak(local)
+    tex8_coherent, tex8_grouped = host.measure_tex_peak(local, u8=True)
+    # dominant kernel = the sweep kernel of the finest level (R8 texels there when the images allow it)
+    top = len(sizes) - 1
+    top_u8 = bool(level_u8.get(top, False))
+    top_sweep_s = level_tm_timed[top]["sweeps_ms"] * 1e-3
+    top_fetches = ncc_level[top]["sweeps"] * 36 * args.steps
+    top_launches = 4 * 4 * len(owned) * args.steps
+    top_peak, top_grouped = (tex8_coherent, tex8_grouped) if top_u8 else (tex_coherent, tex_grouped)
+    top_achieved = top_fetches / top_sweep_s / 1e9
+    per_level = []
+    for lv in range(len(sizes)):
+        s_ms = level_tm_timed[lv]["sweeps_ms"]
+        per_level.append({"level": lv, "size": list(sizes[lv]), "texels": "R8 unorm" if level_u8.get(lv) else "R32F",
+                          "sweeps_ms_per_step": s_ms / args.steps, "init_ms_per_step": level_tm_timed[lv]["init_ms"] / args.steps,
+                          "gfetch_per_s": ncc_level[lv]["sweeps"] * 36 * args.steps / (s_ms * 1e-3) / 1e9})
     hpv = hyp_evals_per_view(sizes)
     views_per_s = n * args.steps / (ms_dev * 1e-3)
     e2e_views_per_s = n * args.steps / (ms_e2e * 1e-3)
@@ -236,6 +279,7 @@ def run_ours(args):
         "config": {"workload": f"configs[2]: DTU-shape {W}x{H} x {n} views, {args.nsrc} sources, full ACMMP "
                                f"({len(sizes)} scales x (photometric+planar prior, geom x2))",
                    "levels": [list(s) for s in sizes], "sharding": f"view % {world}", "exchange": "nccl all_gather of depth maps per stage",
+                   "texels": [p["texels"] for p in per_level],
                    "l2": "inputs (49 x 7.7 MB images + per-view state) exceed the 126 MB L2; no explicit flush",
                    "hyp_evals_per_view": hpv},
         "mpix_hyp_per_s": views_per_s * hpv / 1e6,
@@ -243,17 +287,24 @@ def run_ours(args):
                 "ms_per_step": ms_e2e / args.steps, "mpix_hyp_per_s": e2e_views_per_s * hpv / 1e6},
         "gpu_launches": int(launches),
         "kernel_ms_per_step": {k: tm[k] / args.steps for k in ("init_ms", "sweeps_ms", "tail_ms", "total_ms")},
-        "roofline": {"bound": "tex", "kernel": "sweep_kernel", "achieved": tex_achieved, "peak": tex_coherent, "unit": "Gfetch/s",
-                     "frac": tex_achieved / tex_coherent, "traffic": SWEEP_DRAM_BYTES_PER_LAUNCH,
-                     "launches": n_sweep_launches, "avg_launch_ms": tm["sweeps_ms"] / n_sweep_launches,
-                     "fetches_per_launch": fetches / n_sweep_launches, "peak_grouped_access": tex_grouped,
+        "roofline": {"bound": "tex", "kernel": "sweep_kernel<%s> at %dx%d" % ("R8" if top_u8 else "R32F", sizes[top][0], sizes[top][1]),
+                     "achieved": top_achieved, "peak": top_peak, "unit": "Gfetch/s",
+                     "frac": top_achieved / top_peak, "traffic": SWEEP_DRAM_BYTES_PER_LAUNCH_U8 if top_u8 else SWEEP_DRAM_BYTES_PER_LAUNCH,
+                     "launches": top_launches, "avg_launch_ms": level_tm_timed[top]["sweeps_ms"] / top_launches,
+                     "fetches_per_launch": top_fetches / top_launches, "peak_grouped_access": top_grouped,
+                     "share_of_kernel_time": level_tm_timed[top]["sweeps_ms"] / tm["total_ms"],
+                     "all_levels": {"achieved": tex_achieved, "launches": n_sweep_launches, "avg_launch_ms": tm["sweeps_ms"] / n_sweep_launches,
+                                    "per_level": per_level,
+                                    "peaks": {"R32F": {"coherent": tex_coherent, "grouped": tex_grouped},
+                                              "R8": {"coherent": tex8_coherent, "grouped": tex8_grouped}}},
                      "fp32": {"achieved": fp32_achieved, "peak": fp32_tflops, "unit": "TFLOP/s", "frac": fp32_achieved / fp32_tflops,
                               "mufu_gops_measured": mufu_gops},
                      "ncc_evals_per_step": {"init": ncc["init"], "sweeps": ncc["sweeps"], "reference_formulation": ncc_sweeps // args.steps},
                      "note": "texture-pipe bound (ncu: l1tex data-stage is the top unit; HBM traffic is ~0.7 % of peak, no tensor-shaped work): "
                              "achieved = bilinear fetches issued by sweep_kernel (device-counted NCC evaluations x 36) / its time from CUDA events "
-                             "on the launching stream; peak = fetch rate of tex_peak_kernel measured live on this GPU with warp-coherent "
-                             "coordinates (peak_grouped_access: same with the kernel's 8-hypotheses-per-pixel shape). fp32: SURVEY.md 8(d)'s "
+                             "on the launching stream, for the launches of the finest level (the dominant kernel; all_levels has the rest); "
+                             "peak = fetch rate of tex_peak_kernel measured live on this GPU with warp-coherent "
+                             "coordinates on the same texel format (peak_grouped_access: same with the kernel's 8-hypotheses-per-pixel shape). fp32: SURVEY.md 8(d)'s "
                              "reference-formulation flop (NCC x 1538) against the live FP32 FMA peak. traffic = dram bytes per launch from the "
                              "ncu --set full capture in profiles/ (1600x1200 level)"},
         "clocks": clocks.summary(),

@@ -88,6 +88,16 @@ typedef enum {
     ACMMP_COMPAT_UPSTREAM = 1
 } acmmp_compat_mode;
 
+/* Texel format of the views' layered texture (the reference: one R32F cudaArray per image,
+ * ACMMP.cpp:638-663).  AUTO stores decoded 8-bit grey images that were not resized as R8 unorm
+ * texels - a quarter of the texture footprint - whenever every image of the problem / pyramid
+ * level holds integer grey levels 0..255, and R32F otherwise; the bilinear samples the kernels
+ * see are bit-identical either way (acmmp_b200/csrc/ncc.cuh, tools/tex_u8_probe.cu). */
+typedef enum {
+    ACMMP_TEX_R32F = 0,
+    ACMMP_TEX_AUTO = 1
+} acmmp_tex_format;
+
 typedef struct acmmp_ctx acmmp_ctx;
 
 /* ---- lifetime ------------------------------------------------------------
@@ -109,6 +119,10 @@ int acmmp_set_geom_consistency(acmmp_ctx *ctx, int multi_geometry);
 int acmmp_set_hierarchy(acmmp_ctx *ctx);
 int acmmp_set_planar_prior_params(acmmp_ctx *ctx);
 int acmmp_set_compat_mode(acmmp_ctx *ctx, int mode);
+/* acmmp_tex_format for the following acmmp_set_problem calls (default ACMMP_TEX_R32F);
+ * acmmp_texture_is_u8: 1 when the current problem's views sit in R8 texels. */
+int acmmp_set_texture_format(acmmp_ctx *ctx, int format);
+int acmmp_texture_is_u8(const acmmp_ctx *ctx);
 int acmmp_get_params(const acmmp_ctx *ctx, acmmp_params *out);
 
 /* ---- inputs ----------------------------------------------------------------
@@ -245,10 +259,15 @@ int acmmp_measure_fp32_peak(int device, double *tflops, double *mufu_gops);
  * DTU-shape problem: warp-coherent coordinates, and the propagation kernel's
  * access shape (8 hypotheses around each of 4 pixels per warp). */
 int acmmp_measure_tex_peak(int device, double *coherent_gfetch, double *grouped_gfetch);
+/* the same on R8 unorm texels incl. the rounding of the kU8 kernels (ACMMP_TEX_AUTO levels) */
+int acmmp_measure_tex_peak_u8(int device, double *coherent_gfetch, double *grouped_gfetch);
 /* n bilinear fetches at (xs[i], ys[i]) (unnormalised, texel centres at +0.5) from a host image
  * through the texture set-up of the problem's views (reference: ACMMP.cpp:646-663).  Known-answer
  * hook for the filter emulation of the test oracle (oracle/cost.c: orc_tex_bilinear). */
 int acmmp_tex_sample(int device, const float *image, int width, int height, const float *xs, const float *ys, int n, float *out);
+/* the same through an R8 unorm texture + the rounding of the kU8 kernels (ACMMP_TEX_AUTO): image must hold
+ * integer grey levels 0..255 (ACMMP_ERR_INVALID otherwise); equals acmmp_tex_sample bit for bit. */
+int acmmp_tex_sample_u8(int device, const float *image, int width, int height, const float *xs, const float *ys, int n, float *out);
 
 /* ==== whole-scan schedule ======================================================
  * The stage graph of main() (/root/reference/src/main_ACMMP.cpp:89-176) over a
@@ -284,6 +303,11 @@ const char *acmmp_scan_last_error(const acmmp_scan *s);
  * convertTo CV_32F, ACMMP.cpp:539-541); host or device pointer. */
 int acmmp_scan_set_image(acmmp_scan *s, int view, const float *gray, int on_device);
 int acmmp_scan_set_shard(acmmp_scan *s, int rank, int world);
+/* acmmp_tex_format of the level-wide texture (default ACMMP_TEX_AUTO: R8 texels on levels where no
+ * view is resized and every image holds integer grey levels); call before acmmp_scan_begin_level.
+ * acmmp_scan_level_is_u8: what the current level uses. */
+int acmmp_scan_set_texture_format(acmmp_scan *s, int format);
+int acmmp_scan_level_is_u8(const acmmp_scan *s);
 /* 0 = Jacobi (default; geom-1 reads the geom-0 maps of all views), 1 = the
  * reference's in-place order dependence (geom-1 reads what earlier views of the
  * same loop already wrote; only meaningful with world == 1). */

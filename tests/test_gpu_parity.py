@@ -200,3 +200,56 @@ def test_oracle_texture_filter_equals_hardware():
     assert same.mean() >= 0.995, same.mean()
     # the rest: one unit in the last place of the largest texel (the filter's internal precision)
     assert np.abs(hw - mine).max() <= 2.0 ** -15, np.abs(hw - mine).max()
+
+
+def test_r8_texels_sample_bit_identical_to_r32f():
+    """ACMMP_TEX_AUTO: an R8 unorm texture of integer grey levels + the rounding back onto the 1/256 grid
+    (ncc.cuh, bilateral_ncc<true>) returns the R32F fetch bit for bit: every (a, b) weight pair on extreme
+    and random texel quads, random coordinates incl. the clamped border, and non-integer images are refused."""
+    rng = np.random.default_rng(11)
+    w, h = 96, 64
+    aa, bb = np.meshgrid(np.arange(256, dtype=np.float32), np.arange(256, dtype=np.float32))
+    img = rng.integers(0, 256, (h, w)).astype(np.float32)
+    # texel quads that stress the rounding: all-255, 255/0 checker, 254/255, 1/0
+    quads = {(10, 20): (255, 255, 255, 255), (30, 20): (255, 0, 0, 255), (50, 20): (254, 255, 255, 254), (70, 20): (1, 0, 0, 1),
+             (10, 40): (0, 255, 255, 0), (30, 40): (128, 127, 127, 128)}
+    xs, ys = [], []
+    for (x0, y0), q in quads.items():
+        img[y0, x0], img[y0, x0 + 1], img[y0 + 1, x0], img[y0 + 1, x0 + 1] = q
+        xs.append(x0 + 0.5 + aa.ravel() / 256.0)
+        ys.append(y0 + 0.5 + bb.ravel() / 256.0)
+    n = 400000
+    xs.append(rng.uniform(-3.0, w + 3.0, n).astype(np.float32))
+    ys.append(rng.uniform(-3.0, h + 3.0, n).astype(np.float32))
+    xs, ys = np.concatenate(xs).astype(np.float32), np.concatenate(ys).astype(np.float32)
+    a = host.tex_sample(img, xs, ys)
+    b = host.tex_sample_u8(img, xs, ys)
+    assert (a.view(np.uint32) == b.view(np.uint32)).all(), int((a.view(np.uint32) != b.view(np.uint32)).sum())
+    with pytest.raises(L.AcmmpError):
+        host.tex_sample_u8(img + 0.25, xs[:16], ys[:16])
+    with pytest.raises(L.AcmmpError):
+        host.tex_sample_u8(img - 1.0, xs[:16], ys[:16])
+
+
+def test_operator_api_r8_texels_are_invisible():
+    """SetTextureFormat(TEX_AUTO): a whole RunPatchMatch on 8-bit images is bit-identical to the R32F run
+    (and R8 texels were really used); images with fractional grey levels fall back to R32F."""
+    sc = make_scene(5, 320, 240, 4, seed=3)
+    ids = [0] + sc["pairs"][0]
+    images = [sc["images"][i] for i in ids]
+    cams = [sc["cams"][i] for i in ids]
+    assert all((im == np.round(im)).all() for im in images)
+    out = {}
+    for fmt in (L.TEX_R32F, L.TEX_AUTO):
+        m = host.ACMMP(0)
+        m.SetTextureFormat(fmt)
+        m.InputInitialization(images, cams)
+        assert m.TextureIsU8() == (fmt == L.TEX_AUTO)
+        m.RunPatchMatch(99)
+        out[fmt] = m.GetMaps()
+        if fmt == L.TEX_AUTO:
+            m.InputInitialization([im + 0.5 for im in images], cams)
+            assert not m.TextureIsU8()
+        m.close()
+    for k in range(3):
+        assert (gu.bits(out[L.TEX_R32F][k]) == gu.bits(out[L.TEX_AUTO][k])).all(), k

@@ -171,16 +171,19 @@ def test_hierarchy_upsample_init_bit_exact_vs_live_reference_kernels():
     ref.close()
 
 
-def run_scan(sc, world=1, seed=77, sequential=False):
+def run_scan(sc, world=1, seed=77, sequential=False, tex_format=None, u8_levels=None):
     """full schedule; world > 1 = logical shards executed one after the other on this
     GPU, exchanging their depth-map segments like the NCCL all-gather would."""
-    scans = [host.Scan(sc["cams"], sc["pairs"], rank=r, world=world, sequential_geom=sequential) for r in range(world)]
+    scans = [host.Scan(sc["cams"], sc["pairs"], rank=r, world=world, sequential_geom=sequential, tex_format=tex_format)
+             for r in range(world)]
     for s in scans:
         for v, im in enumerate(sc["images"]):
             s.set_image(v, im)
     for level in range(scans[0].num_levels()):
         for s in scans:
             s.begin_level(level)
+            if u8_levels is not None:
+                u8_levels.append(s.level_is_u8())
         for stage in range(3):
             for s in scans:
                 s.run_stage(stage, seed)
@@ -223,6 +226,24 @@ def test_full_schedule_recovers_the_scene_and_sharding_is_invisible():
         for k in range(3):
             assert (gu.bits(a[v][k]) == gu.bits(a2[v][k])).all(), ("rerun", v, k)
             assert (gu.bits(a[v][k]) == gu.bits(b[v][k])).all(), ("3 shards", v, k)
+
+
+def test_r8_level_texture_is_invisible():
+    """The finest level of a scan of 8-bit images samples R8 texels by default (ACMMP_TEX_AUTO), the resized
+    coarser level R32F; every map of every view is bit-identical to the all-R32F scan.  Images with fractional
+    grey levels keep R32F on every level."""
+    sc = make_scene(5, 1280, 960, 4, seed=2, device="cuda", span_deg=(10.0, 8.0))
+    lv_auto, lv_f32 = [], []
+    a = run_scan(sc, tex_format=L.TEX_R32F, u8_levels=lv_f32)
+    b = run_scan(sc, u8_levels=lv_auto)
+    assert lv_f32 == [False, False] and lv_auto == [False, True], (lv_f32, lv_auto)
+    for v in range(5):
+        for k in range(3):
+            assert (gu.bits(a[v][k]) == gu.bits(b[v][k])).all(), (v, k)
+    sc["images"] = [im + 0.5 for im in sc["images"]]
+    lv = []
+    run_scan(sc, u8_levels=lv)
+    assert lv == [False, False]
 
 
 @needs_ref
