@@ -28,8 +28,8 @@ FLOP_PER_NCC = 1538.0          # 36 x 38 + 170
 # (ncu --set full, profiles/r1g_sweep_init_full_summary.txt: 311 MB read + 121 MB written, average of 8
 # launches); ~1 % of what HBM could move in that time
 SWEEP_DRAM_BYTES_PER_LAUNCH = 432e6
-# the same for sweep_kernel<R8> (finest level, R8 unorm texels); None until the ncu capture of this round is in profiles/
-SWEEP_DRAM_BYTES_PER_LAUNCH_U8 = None
+# the same for sweep_kernel<R8> (finest level, R8 unorm texels)
+SWEEP_DRAM_BYTES_PER_LAUNCH_U8 = 215e6   # profiles/r1o_sweep_u8_full_summary.txt: 148 MB read + 67 MB written
 HYP_PER_RUN = 29               # 1 (init) + 2 x 14; 30 for the hierarchy (upsample-init) run
 
 

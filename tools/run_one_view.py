@@ -17,11 +17,14 @@ ap.add_argument("--height", type=int, default=1200)
 ap.add_argument("--nsrc", type=int, default=10)
 ap.add_argument("--runs", type=int, default=2)
 ap.add_argument("--device", default="cuda")
+ap.add_argument("--tex", default="auto", choices=["auto", "r32f"], help="texel format of the views (auto: R8 for 8-bit images)")
 args = ap.parse_args()
 sc = make_scene(args.nsrc + 1, args.width, args.height, args.nsrc, seed=1, device=args.device, span_deg=(10.0, 8.0))
 ref = (args.nsrc + 1) // 2
 ids = [ref] + sc["pairs"][ref]
 m = host.ACMMP(0)
+from acmmp_b200 import lib as L  # noqa: E402
+m.SetTextureFormat(L.TEX_AUTO if args.tex == "auto" else L.TEX_R32F)
 m.InputInitialization([sc["images"][i] for i in ids], [sc["cams"][i] for i in ids])
 for r in range(args.runs):
     m.RunPatchMatch(1234)
