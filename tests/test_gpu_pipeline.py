@@ -135,6 +135,49 @@ def test_half_sweeps_step_exact_vs_live_reference_kernels():
 
 
 @needs_ref
+def test_planar_prior_half_sweeps_vs_live_reference_kernels():
+    """planar-prior half sweeps from identical state.  The reference never assigns `plane_hypotheses_now` in
+    these runs (ACMMP.cu:1149) and shadows `depth_now` (:1120); ACMMP_COMPAT_REF_SM100 pins both the way the
+    sm_100 build behaves (tools/prior_ub_probe.py).  The reference repeats itself on 96-99.7 % of the pixels."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    from gpu_parity import gt_planes
+    h, w = 240, 320
+    sc = make_scene(5, w, h, 4, seed=0)
+    images, cams, ids = problem(sc, 0)
+    rs = np.random.default_rng(0)
+    pl = gt_planes(sc, 0, rs, 0.01)
+    masks = np.zeros((h, w), np.uint32)
+    masks[h // 6: 5 * h // 6, w // 6: 5 * w // 6] = 1
+    masks[(rs.random((h, w)) < 0.1)] = 0
+    ref = refbind.RefACMMP(0)
+    ref.set_problem(images, cams)
+    ref.set_flags(geom=0, seeded=0, planar_prior=1, hierarchy=0, upsample=0)
+    ref.set_planes(1, pl)
+    ref.set_scalars(3, masks)
+    ref.run_init(1234)
+    m = host.ACMMP(0)
+    m.SetPlanarPriorParams()
+    m.InputInitialization(images, cams)
+    m.CudaPlanarPriorInitialization(pl, masks)
+    m.run_init(1234)
+    assert (gu.bits(m.get_state()[0]) == gu.bits(ref.get_state()[0])).all()
+    for it in (0, 1):
+        for color in (0, 1):
+            rp0, rc0, rs0, rr0, _ = ref.get_state()
+            m.set_state(rp0, rc0, rs0, rr0)
+            ref.run_sweep(it, color)
+            m.run_sweep(it, color)
+            rp, mp = ref.get_state()[0], m.get_state()[0]
+            inner = interior(h, w, 4) & color_mask(h, w, color)
+            same = (gu.bits(mp) == gu.bits(rp)).all(-1)
+            assert same[inner & (masks > 0)].mean() >= 0.85, (it, color, same[inner & (masks > 0)].mean())
+            assert same[inner & (masks == 0)].mean() >= 0.80, (it, color, same[inner & (masks == 0)].mean())
+            assert same[inner].mean() >= 0.85, (it, color, same[inner].mean())
+    m.close()
+    ref.close()
+
+
+@needs_ref
 def test_hierarchy_upsample_init_bit_exact_vs_live_reference_kernels():
     """RandomInitialization in hierarchy + upsample mode (ACMMP.cu:663-689): joint-bilateral
     upsampling of the coarse normals, cost of the uploaded JBU-depth plane (pre_costs) and of
