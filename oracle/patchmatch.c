@@ -14,8 +14,13 @@
  *    neighbour has not finished yet;
  *  - `float4 plane_hypotheses_now` (ACMMP.cu:1149) is uninitialised unless a
  *    neighbour is adopted in a non-prior run: compat 0 = what the sm_100 build
- *    does (takes the best arm's plane whenever that arm exists, the live plane
- *    otherwise), compat 1 = upstream semantics (refine the live plane).
+ *    does (takes the best arm's plane whenever that arm exists - the arg-min arm,
+ *    or under a planar prior that covers the pixel the arm with the largest
+ *    restricted cost - and the live plane otherwise; measured against the
+ *    reference's kernels with tools/prior_ub_probe.py), compat 1 = upstream
+ *    semantics (refine the live plane).
+ * A defined quirk kept as it is: under a prior the adoption assigns a block-local
+ * `depth_now` that shadows the one handed to the refinement (ACMMP.cu:1120,1129).
  */
 #include <math.h>
 #include <stdlib.h>
@@ -339,27 +344,32 @@ static void sweep_pixel(orc_problem *p, const float *P, const float *C, int iter
             const float dd = orc_plane_depth(rc, plane_c, px, py) - depth_prior;
             const float ac = prior_c[0] * plane_c[0] + prior_c[1] * plane_c[1] + prior_c[2] * plane_c[2];
             const float rnow = expf(-cost_now * cost_now / beta) * prior_factor(dd, ac, tds2, tas2);
+            memcpy(plane_now, live_plane, sizeof plane_now);
             if (flag[max_idx]) {
                 const float *q = P + (size_t)pos[max_idx] * 4;
                 const float db = orc_plane_depth(rc, q, px, py);
                 if (db >= dmin && db <= dmax && rf[max_idx] > rnow) {
-                    depth_now = db;
+                    /* not depth_now: the reference's assignment hits a shadowing local (ACMMP.cu:1120,1129) */
                     memcpy(live_plane, q, sizeof live_plane);
                     live_cost = final_costs[max_idx];
                     restricted_cost = rf[max_idx];
                     write_sel = 1;
                 }
+                memcpy(plane_now, p->compat == 0 ? q : live_plane, sizeof plane_now);
             }
-        } else if (flag[min_idx]) {
-            const float *q = P + (size_t)pos[min_idx] * 4;
-            const float db = orc_plane_depth(rc, q, px, py);
-            if (db >= dmin && db <= dmax && final_costs[min_idx] < cost_now) {
-                depth_now = db;
-                memcpy(live_plane, q, sizeof live_plane);
-                live_cost = final_costs[min_idx];
+        } else {
+            memcpy(plane_now, live_plane, sizeof plane_now);
+            if (flag[min_idx]) {
+                const float *q = P + (size_t)pos[min_idx] * 4;
+                const float db = orc_plane_depth(rc, q, px, py);
+                if (db >= dmin && db <= dmax && final_costs[min_idx] < cost_now) {
+                    depth_now = db;
+                    memcpy(live_plane, q, sizeof live_plane);
+                    live_cost = final_costs[min_idx];
+                }
+                memcpy(plane_now, p->compat == 0 ? q : live_plane, sizeof plane_now);
             }
         }
-        memcpy(plane_now, live_plane, sizeof plane_now);
         if (p->compat == 1) cost_now = live_cost;
     } else if (flag[min_idx]) { /* ACMMP.cu:1149-1159 */
         const float *q = P + (size_t)pos[min_idx] * 4;
