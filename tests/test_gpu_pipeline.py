@@ -332,6 +332,15 @@ def test_full_size_properties_dtu_shape():
     gt = sc["depths"][5]
     assert (np.abs(d1 - gt) / gt < 0.01)[16:-16, 16:-16].mean() >= 0.95
     m.close()
+    # the same run on R8 texels (ACMMP_TEX_AUTO): bit-identical at full size
+    m8 = host.ACMMP(0)
+    m8.SetTextureFormat(L.TEX_AUTO)
+    m8.InputInitialization(images, cams)
+    assert m8.TextureIsU8()
+    m8.RunPatchMatch(1234)
+    d8, n8, c8 = m8.GetMaps()
+    assert (gu.bits(d1) == gu.bits(d8)).all() and (gu.bits(n1) == gu.bits(n8)).all() and (gu.bits(c1) == gu.bits(c8)).all()
+    m8.close()
 
 
 def test_ragged_and_edge_inputs():
