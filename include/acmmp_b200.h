@@ -79,10 +79,12 @@ typedef struct {
 /* How the uninitialised `plane_hypotheses_now` of the reference
  * (ACMMP.cu:1149-1172) is given a meaning.  See DESIGN.md "UB pinning". */
 typedef enum {
-    /* what nvcc 12.9 -arch sm_100 made of it: in non-prior runs the pixel takes
-     * the best neighbour's plane whenever that arm exists (cost / depth / views
-     * only if it is cheaper); where the compiled code reads garbage registers
-     * the current plane is used instead. */
+    /* what nvcc 12.9 -arch sm_100 made of it: the refinement starts from the best
+     * neighbour's plane whenever that arm exists (the arg-min arm; where a planar
+     * prior covers the pixel, the arm with the largest restricted cost), while cost /
+     * depth / views are taken over only if the arm is adopted; where the compiled
+     * code reads garbage registers (the arm does not exist) the current plane is
+     * used instead.  Measured against the reference's kernels: DESIGN.md 4(2). */
     ACMMP_COMPAT_REF_SM100 = 0,
     /* upstream GhiXu/ACMMP semantics: refine the current plane in place. */
     ACMMP_COMPAT_UPSTREAM = 1
