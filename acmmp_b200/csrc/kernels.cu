@@ -415,6 +415,18 @@ cudaError_t launch_pad_replicate(const float *src, int w, int h, float *dst, int
     return cudaGetLastError();
 }
 
+// 8-bit grey -> float (imread GRAYSCALE + convertTo CV_32F, ACMMP.cpp:539-541)
+__global__ void u8_to_float_kernel(const uint8_t *__restrict__ src, size_t n, float *__restrict__ dst) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = (float)src[i];
+}
+cudaError_t launch_u8_to_float(const uint8_t *src, size_t n, float *dst, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    size_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    u8_to_float_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, n, dst);
+    return cudaGetLastError();
+}
+
 // integer grey levels?  (decoded 8-bit images that were never resized)
 __global__ void check_u8_kernel(const float *__restrict__ src, size_t n, int *not_u8) {
     bool bad = false;

@@ -65,6 +65,7 @@ cudaError_t launch_jbu_depth(const float *image, int w, int h, const float *sdep
                              float *out, cudaStream_t st);
 cudaError_t launch_resize_linear(const float *src, int sw, int sh, float *dst, int dw, int dh, cudaStream_t st);
 cudaError_t launch_pad_replicate(const float *src, int w, int h, float *dst, int W, int H, cudaStream_t st);
+cudaError_t launch_u8_to_float(const uint8_t *src, size_t n, float *dst, cudaStream_t st);
 // *not_u8 |= 1 when a pixel of src is not an integer grey level 0..255
 cudaError_t launch_check_u8(const float *src, size_t n, int *not_u8, cudaStream_t st);
 // float grey levels -> bytes, edges replicated up to W x H (the layer size)

@@ -356,6 +356,17 @@ class Scan:
             if sync:
                 self.sync()   # the host array may be released after this returns
 
+    def set_image_u8(self, view, gray, on_device=False, sync=True):
+        """gray: uint8 HxW numpy array (what cv::imread(..., IMREAD_GRAYSCALE) returns) or an int device
+        pointer; converted to float on the device.  sync=False: keep the host array alive until sync()."""
+        if on_device:
+            self._ck(self._lib.acmmp_scan_set_image_u8(self._s, view, C.c_void_p(int(gray)), 1), "set_image_u8")
+        else:
+            g = np.ascontiguousarray(gray, np.uint8)
+            self._ck(self._lib.acmmp_scan_set_image_u8(self._s, view, C.c_void_p(g.ctypes.data), 0), "set_image_u8")
+            if sync:
+                self.sync()
+
     def num_levels(self):
         return self._lib.acmmp_scan_num_levels(self._s)
 

@@ -98,6 +98,8 @@ public:
     Scan(const Scan &) = delete;
     Scan &operator=(const Scan &) = delete;
     void SetImage(int view, const Map<float> &gray) { check(acmmp_scan_set_image(s_, view, gray.data.data(), 0)); check(acmmp_scan_sync(s_)); }
+    // the 8-bit grey image as cv::imread(path, IMREAD_GRAYSCALE) returns it; converted to float on the device
+    void SetImageU8(int view, const Map<uint8_t> &gray) { check(acmmp_scan_set_image_u8(s_, view, gray.data.data(), 0)); check(acmmp_scan_sync(s_)); }
     // seeded mode (-p): the 16-bit prior images of a view in cv::imread(path, -1) order (pSampler, acmmp_definitions.cpp:98-131)
     void SetPriorMaps(int view, const Map<uint16_t> &depth16, const Map<uint16_t> &normal16) {
         if (depth16.channels != 1 || normal16.channels < 3 || normal16.rows != depth16.rows || normal16.cols != depth16.cols)

@@ -254,6 +254,16 @@ inline Map<float> ToGrayFloat(const Map<uint8_t> &im) {
     return g;
 }
 
+// the same before the convertTo: the 8-bit grey image (handed to acmmp_scan_set_image_u8, which converts on the device)
+inline Map<uint8_t> ToGray8(const Map<uint8_t> &im) {
+    if (im.channels == 1) return im;
+    Map<uint8_t> g(im.rows, im.cols, 1);
+    const size_t n = (size_t)im.rows * im.cols;
+    for (size_t i = 0; i < n; ++i)
+        g.data[i] = (uint8_t)((im.data[3 * i] * 1868 + im.data[3 * i + 1] * 9617 + im.data[3 * i + 2] * 4899 + 8192) >> 14);
+    return g;
+}
+
 // binary little-endian PLY, vertex = x y z nx ny nz (float) red green blue (uchar); points9 as
 // acmmp_fusion_get_points returns them (colour = stored BGR bytes): the reference writes
 // red = c2, green = c1, blue = c0 (ACMMP.cpp:411-430)

@@ -136,9 +136,12 @@ def run_ours(args):
     sc = make_scan_inputs(args, dev)
     n = args.views
     imgs_dev = [im.contiguous().float() for im in sc["images"]]
-    imgs_host = [torch.empty(im.shape, dtype=torch.float32).pin_memory() for im in imgs_dev]
+    # e2e input = what the reference reads: 8-bit grey images (cv::imread GRAYSCALE), in pinned host memory;
+    # the float conversion of ACMMP.cpp:541 runs on the device (acmmp_scan_set_image_u8)
+    imgs_host = [torch.empty(im.shape, dtype=torch.uint8).pin_memory() for im in imgs_dev]
     for h_, d_ in zip(imgs_host, imgs_dev):
-        h_.copy_(d_)
+        assert bool((d_ == d_.round()).all()) and float(d_.min()) >= 0 and float(d_.max()) <= 255
+        h_.copy_(d_.to(torch.uint8))
     torch.cuda.synchronize()
     imgs_np = [t.numpy() for t in imgs_host]
     from acmmp_b200 import lib as L
@@ -177,7 +180,7 @@ def run_ours(args):
         scan.reset()
         for v in range(n):
             if e2e:
-                scan.set_image(v, imgs_np[v], sync=False)
+                scan.set_image_u8(v, imgs_np[v], sync=False)
             else:
                 scan.set_image(v, imgs_dev[v].data_ptr(), on_device=True)
         scan.run_all(seed=1234, exchange=exchange, level_done=level_done)
@@ -269,7 +272,7 @@ def run_ours(args):
     fetches = ncc["sweeps"] * 36 * args.steps
     tex_achieved = fetches / sweep_s / 1e9
     n_sweep_launches = 4 * 4 * len(owned) * len(sizes) * args.steps   # 4 runs x 4 half-sweeps per view per level
-    h2d = sum(int(np.prod(im.shape)) * 4 for im in imgs_np)
+    h2d = sum(int(np.prod(im.shape)) for im in imgs_np)   # uint8
     d2h = len(owned) * H * W * 5 * 4
     line = {
         "metric": "views/s, DTU-shape 1600x1200 49-view full ACMMP (multi-scale + planar prior + geometric consistency)",

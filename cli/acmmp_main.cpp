@@ -130,7 +130,7 @@ int main(int argc, char **argv) {
         mkdir(output_folder.c_str(), 0777);
 
         Scan scan(cams, pairs, device);
-        for (int i = 0; i < n; ++i) scan.SetImage(i, ToGrayFloat(images[i]));
+        for (int i = 0; i < n; ++i) scan.SetImageU8(i, ToGray8(images[i]));
         if (prior) {
             // the reference numbers the prior images by problem index, not by image id (acmmp_definitions.cpp:278, :104-105)
             for (int i = 0; i < n; ++i) {

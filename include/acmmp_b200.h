@@ -304,6 +304,10 @@ const char *acmmp_scan_last_error(const acmmp_scan *s);
 /* full-resolution grey image of one view as float (imread GRAYSCALE +
  * convertTo CV_32F, ACMMP.cpp:539-541); host or device pointer. */
 int acmmp_scan_set_image(acmmp_scan *s, int view, const float *gray, int on_device);
+/* the same from the 8-bit image itself (what cv::imread(path, IMREAD_GRAYSCALE) returns, before the
+ * reference's convertTo(CV_32F)): a quarter of the host-to-device bytes; the conversion runs on the
+ * device.  Identical results to acmmp_scan_set_image of the converted image. */
+int acmmp_scan_set_image_u8(acmmp_scan *s, int view, const uint8_t *gray, int on_device);
 int acmmp_scan_set_shard(acmmp_scan *s, int rank, int world);
 /* acmmp_tex_format of the level-wide texture (default ACMMP_TEX_AUTO: R8 texels on levels where no
  * view is resized and every image holds integer grey levels); call before acmmp_scan_begin_level.

@@ -214,14 +214,17 @@ def test_hierarchy_upsample_init_bit_exact_vs_live_reference_kernels():
     ref.close()
 
 
-def run_scan(sc, world=1, seed=77, sequential=False, tex_format=None, u8_levels=None):
+def run_scan(sc, world=1, seed=77, sequential=False, tex_format=None, u8_levels=None, upload_u8=False):
     """full schedule; world > 1 = logical shards executed one after the other on this
     GPU, exchanging their depth-map segments like the NCCL all-gather would."""
     scans = [host.Scan(sc["cams"], sc["pairs"], rank=r, world=world, sequential_geom=sequential, tex_format=tex_format)
              for r in range(world)]
     for s in scans:
         for v, im in enumerate(sc["images"]):
-            s.set_image(v, im)
+            if upload_u8:
+                s.set_image_u8(v, np.asarray(im).astype(np.uint8))
+            else:
+                s.set_image(v, im)
     for level in range(scans[0].num_levels()):
         for s in scans:
             s.begin_level(level)
@@ -283,6 +286,11 @@ def test_r8_level_texture_is_invisible():
     for v in range(5):
         for k in range(3):
             assert (gu.bits(a[v][k]) == gu.bits(b[v][k])).all(), (v, k)
+    # the 8-bit upload (acmmp_scan_set_image_u8) is the same scan
+    c = run_scan(sc, upload_u8=True)
+    for v in range(5):
+        for k in range(3):
+            assert (gu.bits(a[v][k]) == gu.bits(c[v][k])).all(), ("u8 upload", v, k)
     sc["images"] = [im + 0.5 for im in sc["images"]]
     lv = []
     run_scan(sc, u8_levels=lv)
