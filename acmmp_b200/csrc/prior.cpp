@@ -12,12 +12,22 @@
 // is unique up to the diagonal chosen inside co-circular quads; triangle ORDER
 // (which only decides who wins a raster pixel shared by two triangles,
 // acmmp_definitions.cpp:346-352) is by smallest edge index here.
+//
+// The top levels of the recursion run on separate threads, each half in its own
+// edge arena; appending the right arena to the left one reproduces exactly the edge
+// numbering of the sequential recursion (left subtree, right subtree, merge), so the
+// triangles and their order do not depend on the number of threads.
 #include "prior.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cstdint>
+#include <future>
 #include <numeric>
+#include <thread>
 #include <vector>
+
+#include <stdlib.h>
 
 namespace acmmp {
 namespace {
@@ -73,10 +83,11 @@ struct QuadEdges {
 struct Triangulator {
     const std::vector<Pt> &p;
     QuadEdges q;
-    explicit Triangulator(const std::vector<Pt> &pts) : p(pts) {
-        q.onext.reserve(pts.size() * 16);
-        q.org.reserve(pts.size() * 16);
-        q.dead.reserve(pts.size() * 4);
+    // npts: points this arena will hold edges for (~3 edges per point + removed ones, 4 slots per edge)
+    Triangulator(const std::vector<Pt> &pts, size_t npts) : p(pts) {
+        q.onext.reserve(npts * 16);
+        q.org.reserve(npts * 16);
+        q.dead.reserve(npts * 4);
     }
     // > 0 when a, b, c make a left turn (in a y-up frame)
     int64_t orient(int a, int b, int c) const {
@@ -95,6 +106,35 @@ struct Triangulator {
     bool right_of(int x, int e) const { return ccw(x, q.dest(e), q.org[e]); }
     bool left_of(int x, int e) const { return ccw(x, q.org[e], q.dest(e)); }
     bool valid(int e, int basel) const { return right_of(q.dest(e), basel); }
+
+    // other's edges appended behind this arena's; returns the offset added to other's edge ids
+    int append(const QuadEdges &o) {
+        const int off = (int)q.onext.size();
+        q.onext.resize(off + o.onext.size());
+        for (size_t i = 0; i < o.onext.size(); ++i) q.onext[off + i] = o.onext[i] + off;
+        q.org.insert(q.org.end(), o.org.begin(), o.org.end());
+        q.dead.insert(q.dead.end(), o.dead.begin(), o.dead.end());
+        return off;
+    }
+
+    // build(lo, hi) with the two halves of the top `depth` levels triangulated concurrently
+    void build_parallel(int lo, int hi, int depth, int &le, int &re) {
+        const int n = hi - lo;
+        if (depth <= 0 || n < 4096 || !q.onext.empty()) {
+            build(lo, hi, le, re);
+            return;
+        }
+        const int mid = lo + n / 2;
+        Triangulator R(p, (size_t)(hi - mid));
+        int ldo, ldi, rdi, rdo;
+        auto right = std::async(std::launch::async, [&] { R.build_parallel(mid, hi, depth - 1, rdi, rdo); });
+        build_parallel(lo, mid, depth - 1, ldo, ldi);
+        right.get();
+        const int off = append(R.q);
+        rdi += off;
+        rdo += off;
+        merge(ldo, ldi, rdi, rdo, le, re);
+    }
 
     void build(int lo, int hi, int &le, int &re) {
         const int n = hi - lo;
@@ -125,6 +165,11 @@ struct Triangulator {
         int ldo, ldi, rdi, rdo;
         build(lo, mid, ldo, ldi);
         build(mid, hi, rdi, rdo);
+        merge(ldo, ldi, rdi, rdo, le, re);
+    }
+
+    // joins the triangulations of two x-separated halves (Guibas & Stolfi, fig. 23)
+    void merge(int ldo, int ldi, int rdi, int rdo, int &le, int &re) {
         for (;;) {   // lower common tangent
             if (left_of(q.org[rdi], ldi)) ldi = q.lnext(ldi);
             else if (right_of(q.org[ldi], rdi)) rdi = q.rprev(rdi);
@@ -162,7 +207,27 @@ struct Triangulator {
     }
 };
 
+std::atomic<int> g_threads{0};   // 0 = from the host's core count
+
+// 2^depth threads for the top of the recursion
+int delaunay_parallel_depth() {
+    int t = g_threads.load();
+    if (t <= 0) {
+        // the scan runs up to three triangulations at once (software pipeline, capi_scan.cu.inc)
+        static const int hw = [] {
+            if (const char *e = getenv("ACMMP_DELAUNAY_THREADS")) return atoi(e);
+            return (int)(std::thread::hardware_concurrency() / 3);
+        }();
+        t = hw;
+    }
+    int d = 0;
+    while (d < 3 && (2 << d) <= t) ++d;
+    return d;
+}
+
 }  // namespace
+
+void delaunay_set_threads(int threads) { g_threads.store(threads < 0 ? 0 : threads); }
 
 int delaunay_triangulate(const int32_t *xy, int n, std::vector<int32_t> &tris) {
     tris.clear();
@@ -174,9 +239,9 @@ int delaunay_triangulate(const int32_t *xy, int n, std::vector<int32_t> &tris) {
               pts.end());
     const int m = (int)pts.size();
     if (m < 3) return 0;
-    Triangulator T(pts);
+    Triangulator T(pts, pts.size());
     int le, re;
-    T.build(0, m, le, re);
+    T.build_parallel(0, m, delaunay_parallel_depth(), le, re);
     const QuadEdges &q = T.q;
     const int ne = (int)q.onext.size();
     tris.reserve((size_t)m * 6);

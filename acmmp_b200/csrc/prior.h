@@ -17,5 +17,8 @@ namespace acmmp {
 // Delaunay triangulation of n integer points (x0,y0,x1,y1,...).  Appends
 // 6 ints per triangle (x,y of the three vertices) to `tris`; returns the count.
 int delaunay_triangulate(const int32_t *xy, int n, std::vector<int32_t> &tris);
+// threads one triangulation may use for the top of its recursion (1 = sequential, 0 = a third of the
+// host's cores, capped at 8); the result does not depend on it
+void delaunay_set_threads(int threads);
 
 }  // namespace acmmp

@@ -181,6 +181,10 @@ int acmmp_get_planar_prior(acmmp_ctx *ctx, float *planes4, uint32_t *mask);
  * triangle count (>= 0) or a negative status.  Pure host code: no device
  * needed. */
 int acmmp_delaunay(const int32_t *xy, int n, int32_t *tris, int capacity);
+/* host threads one triangulation may use (the top levels of the divide-and-conquer recursion run
+ * concurrently): 1 = sequential, 0 = default (a third of the host's cores, at most 8; environment
+ * variable ACMMP_DELAUNAY_THREADS overrides).  Triangles and their order do not depend on it. */
+int acmmp_set_delaunay_threads(int threads);
 
 /* ---- run -------------------------------------------------------------------
  * ACMMP::RunPatchMatch (ACMMP.cu:1378-1456).  `seed` replaces the reference's

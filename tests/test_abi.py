@@ -92,3 +92,31 @@ def test_delaunay_edge_cases():
     assert len(host.DelaunayTriangulation([[0, 0], [5, 5], [10, 10], [15, 15]])) == 0     # collinear
     assert len(host.DelaunayTriangulation([[0, 0], [5, 0], [0, 5], [0, 0]])) == 1          # duplicate dropped
     assert len(host.DelaunayTriangulation([[0, 0], [5, 0], [0, 5], [5, 5]])) == 2          # co-circular square
+
+
+def test_delaunay_does_not_depend_on_the_thread_count():
+    """the top levels of the divide-and-conquer recursion run on separate threads, each half in its own edge
+    arena; appended arenas reproduce the sequential edge numbering, so triangles AND their order (which decides
+    the raster overwrite, acmmp_definitions.cpp:346-352) are identical for any thread count."""
+    lib = L.load()
+    rng = np.random.default_rng(3)
+    cases = []
+    # support points as the planar prior makes them: one per 5 x 5 cell, ~15 % of the cells empty
+    for w, h in ((1600, 1200), (640, 480)):
+        cy, cx = np.mgrid[0:h // 5, 0:w // 5]
+        keep = rng.random(cx.shape) > 0.15
+        pts = np.stack([cx[keep] * 5 + rng.integers(0, 5, keep.sum()), cy[keep] * 5 + rng.integers(0, 5, keep.sum())], -1)
+        cases.append(pts[rng.permutation(len(pts))])
+    cases.append(np.stack(np.meshgrid(np.arange(0, 400, 5), np.arange(0, 300, 5)), -1).reshape(-1, 2))   # exact grid: all co-circular
+    cases.append(rng.integers(0, 3000, (20000, 2)))
+    try:
+        for pts in cases:
+            assert lib.acmmp_set_delaunay_threads(1) == 0
+            a = host.DelaunayTriangulation(pts)
+            for t in (2, 4, 8, 64):
+                assert lib.acmmp_set_delaunay_threads(t) == 0
+                b = host.DelaunayTriangulation(pts)
+                assert a.shape == b.shape and (a == b).all(), (len(pts), t)
+    finally:
+        lib.acmmp_set_delaunay_threads(0)
+    assert lib.acmmp_set_delaunay_threads(-1) != 0
