@@ -373,12 +373,60 @@ def run_ours(args):
             line["fusion"].update({"cpu_port_s": time.time() - t0, "cpu_port_points": int(cnt), "cpu_cores": 1})
         fus.close()
     if rank == 0 and not args.no_cpu_baseline:
+        line["planar_prior"] = planar_prior_baseline(args, sc)
         line["cpu_baseline"] = cpu_baseline(args, sc, hpv)
     if rank == 0:
         print(json.dumps(line), flush=True)
     scan.close()
     if dist is not None:
         dist.destroy_process_group()
+
+
+def planar_prior_baseline(args, sc):
+    """The second baseline north_star names: the reference's CPU planar-prior code (GetSupportPoints ->
+    Delaunay -> triangle raster + plane fit + range check, ACMMP.cpp:868-958, acmmp_definitions.cpp:306-378),
+    restated in oracle/prior.c, on one host core for ONE view, next to the product's construction of the
+    same prior (support cells, raster, plane fit and range check as kernels; Delaunay on the host).
+    Outside the timed region; the scan's 98 prior constructions per step are inside `value`."""
+    import oraclebind as ob
+    from acmmp_b200 import host, lib as L
+    v = args.views // 2
+    ids = [v] + sc["pairs"][v]
+    to_np = lambda t: t.detach().float().cpu().numpy() if hasattr(t, "detach") else np.asarray(t, np.float32)
+    images = [to_np(sc["images"][i]) for i in ids]
+    cams = [sc["cams"][i] for i in ids]
+    m = host.ACMMP(0)
+    m.SetTextureFormat(L.TEX_AUTO)
+    m.InputInitialization(images, cams)
+    m.RunPatchMatch(1234)
+    depth, _, cost = m.GetMaps()
+    pr = m.params()
+    dev_ms = []
+    for _ in range(3):
+        t0 = time.time()
+        ns, nt = m.BuildPlanarPrior()
+        m.sync()
+        dev_ms.append((time.time() - t0) * 1e3)
+    _, mask = m.GetPlanarPrior()
+    lib = L.load()
+    lib.acmmp_set_delaunay_threads(1)   # the reference's cv::Subdiv2D is single-threaded
+    try:
+        t0 = time.time()
+        pts = ob.support_points(cost)
+        t1 = time.time()
+        tris = host.DelaunayTriangulation(pts)
+        t2 = time.time()
+        _, mask_o, _ = ob.prior_from_triangles(cams[0], depth, tris.reshape(-1, 6), pr.depth_min, pr.depth_max)
+        t3 = time.time()
+    finally:
+        lib.acmmp_set_delaunay_threads(0)
+    m.close()
+    return {"what": "planar-prior construction of one %dx%d view" % (args.width, args.height), "support_points": int(ns), "triangles": int(nt),
+            "ours_ms": min(dev_ms), "cpu_port_ms": (t3 - t0) * 1e3, "cpu_cores": 1,
+            "cpu_port_breakdown_ms": {"support_points": (t1 - t0) * 1e3,
+                                      "delaunay (the product's host code on 1 thread; the reference calls cv::Subdiv2D)": (t2 - t1) * 1e3,
+                                      "raster + plane fit + range check": (t3 - t2) * 1e3},
+            "labels_equal_frac": float((mask == mask_o).mean())}
 
 
 def cpu_baseline(args, sc, hyp_per_view):
