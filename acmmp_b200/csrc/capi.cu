@@ -90,6 +90,7 @@ struct acmmp_ctx {
     std::string error;
     acmmp_params params;
     int compat = ACMMP_COMPAT_REF_SM100;
+    int wave_blocks = 0;   // acmmp_set_wave_emulation: resident blocks of the reference launch (0 = off)
     int n = 0;   // images in the problem
     int W = 0, H = 0;
     std::vector<acmmp_camera> cams;
@@ -476,6 +477,12 @@ int acmmp_set_compat_mode(acmmp_ctx *ctx, int mode) {
     if (mode != ACMMP_COMPAT_REF_SM100 && mode != ACMMP_COMPAT_UPSTREAM)
         return fail(ctx, ACMMP_ERR_INVALID, "unknown compat mode %d", mode);
     ctx->compat = mode;
+    return 0;
+}
+int acmmp_set_wave_emulation(acmmp_ctx *ctx, int resident_blocks) {
+    if (!ctx) return ACMMP_ERR_INVALID;
+    if (resident_blocks < 0) return fail(ctx, ACMMP_ERR_INVALID, "resident_blocks must be >= 0");
+    ctx->wave_blocks = resident_blocks;
     return 0;
 }
 int acmmp_set_texture_format(acmmp_ctx *ctx, int format) {

@@ -342,12 +342,11 @@ cudaError_t launch_init(const InitLaunch &L, cudaStream_t st) {
     a.hierarchy = L.hierarchy; a.top_k = L.top_k; a.sigma_spatial = L.sigma_spatial; a.sigma_color = L.sigma_color;
     a.scaled_cols = L.scaled_cols; a.scaled_rows = L.scaled_rows;
     const size_t smem = init_smem_bytes(L.nsrc);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(init_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(init_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // the opt-in is a per-device attribute and contexts may live on several devices of one process:
+    // set it on every large launch (a host-side table look-up next to a kernel launch)
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(L.tex_u8 ? init_kernel<true> : init_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        configured = smem;
     }
     if (L.tex_u8) init_kernel<true><<<grid2(L.W, L.H, kInitTileW, kInitTileH), kInitThreads, smem, st>>>(a);
     else init_kernel<false><<<grid2(L.W, L.H, kInitTileW, kInitTileH), kInitThreads, smem, st>>>(a);
@@ -356,7 +355,8 @@ cudaError_t launch_init(const InitLaunch &L, cudaStream_t st) {
 
 cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st) {
     SweepArgs a;
-    a.planes_in = L.planes_in; a.costs_in = L.costs_in; a.planes = L.planes; a.costs = L.costs;
+    a.planes_in = L.planes_in; a.costs_in = L.costs_in; a.planes_self = L.planes_self; a.costs_self = L.costs_self;
+    a.planes = L.planes; a.costs = L.costs;
     a.selected_views = L.selected_views; a.pre_costs = L.pre_costs; a.prior_planes = L.prior_planes;
     a.plane_masks = L.plane_masks;
     a.rng = RngPlanes{L.rng6, (size_t)L.W * L.H};
@@ -364,14 +364,13 @@ cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st) {
     a.sigma_spatial = L.sigma_spatial; a.sigma_color = L.sigma_color;
     a.geom_consistency = L.geom_consistency; a.planar_prior = L.planar_prior; a.hierarchy = L.hierarchy;
     a.compat = L.compat;
+    a.wave_lo = L.wave_lo; a.wave_hi = L.wave_hi; a.ref_grid_x = L.ref_grid_x;
     a.ncc_counter = L.ncc_counter;
     const size_t smem = sweep_smem_bytes(L.nsrc);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(sweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(sweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // per-device attribute: see launch_init
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(L.tex_u8 ? sweep_kernel<true> : sweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        configured = smem;
     }
     if (L.tex_u8) sweep_kernel<true><<<grid2(L.W, L.H, kTileW, kTileH), kSweepThreads, smem, st>>>(a);
     else sweep_kernel<false><<<grid2(L.W, L.H, kTileW, kTileH), kSweepThreads, smem, st>>>(a);

@@ -32,6 +32,8 @@ struct InitLaunch {
 struct SweepLaunch {
     const float4 *planes_in;
     const float *costs_in;
+    const float4 *planes_self;
+    const float *costs_self;
     float4 *planes;
     float *costs;
     uint32_t *selected_views;
@@ -47,6 +49,7 @@ struct SweepLaunch {
     int W, H, nsrc, iter, color;
     float sigma_spatial, sigma_color;
     int geom_consistency, planar_prior, hierarchy, compat;
+    int wave_lo, wave_hi, ref_grid_x;   // wave emulation (sweep_kernel.cuh); wave_hi == 0: off
     unsigned long long *ncc_counter;   // nullable; 4096 slots
 };
 

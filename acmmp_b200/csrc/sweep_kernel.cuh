@@ -23,9 +23,11 @@
 //  * the XORWOW state stays in registers for the whole sweep (every lane of a
 //    group carries an identical copy, so all lanes make the same draws).
 //  * same-colour reads (the V-shaped near-arm candidates sit on the colour
-//    being rewritten, a data race in the reference) come from a snapshot of
-//    planes/costs taken before the launch: deterministic, and what the
-//    reference does whenever the neighbour has not finished yet.
+//    being rewritten, a data race in the reference) see the state before the
+//    launch: planes / costs are ping-pong buffers (read one, write the other,
+//    the other colour's pixels are copied across by the same CTA), which is
+//    deterministic and what the reference does whenever the neighbour has not
+//    finished yet.
 #pragma once
 #include "common.cuh"
 #include "geometry.cuh"
@@ -46,9 +48,15 @@ constexpr int kInitGroups = kInitTileW * kInitTileH;   // pixels per CTA
 constexpr int kInitThreads = kInitGroup * kInitGroups;
 
 struct SweepArgs {
-    // snapshot (read) and live (write) state
-    const float4 *planes_in;
-    const float *costs_in;
+    // State before the half-sweep (read) and after it (write).  Production: ping-pong - `planes_in` ==
+    // `planes_self` is the state before, `planes` the other buffer; the kernel writes its colour's pixels
+    // and copies the other colour's across, so no snapshot copy is needed.  Diagnostics
+    // (acmmp_run_sweep_snapshot): neighbour reads from an injected snapshot, centre from the live state,
+    // written in place (`planes` == `planes_self`).
+    const float4 *planes_in;     // neighbour planes (candidates of the 8 arms)
+    const float *costs_in;       // neighbour costs
+    const float4 *planes_self;   // the pixel's own plane; source of the other colour's copy
+    const float *costs_self;
     float4 *planes;
     float *costs;
     uint32_t *selected_views;
@@ -66,6 +74,13 @@ struct SweepArgs {
     float sigma_spatial, sigma_color;
     int geom_consistency, planar_prior, hierarchy;
     int compat;               // acmmp_compat_mode
+    // Emulation of the reference launch's block waves (acmmp_set_wave_emulation; 0 = off).  The reference
+    // covers the image with 32 x 32-pixel blocks (32 x 16 threads, one colour) of which `resident` run at a
+    // time (148 on a B200: one 512-thread block of 128 registers per SM); blocks of a later wave start when
+    // those of the earlier wave have finished and stored their results, so their same-colour reads of earlier
+    // blocks see NEW planes / costs.  This sub-launch handles the reference blocks [wave_lo, wave_hi) and reads
+    // same-colour neighbours in blocks < wave_lo from the output buffers.
+    int wave_lo, wave_hi, ref_grid_x;
     unsigned long long *ncc_counter;   // optional instrumentation: kNccCounterSlots slots, NCC evaluations issued
 };
 constexpr int kNccCounterSlots = 4096;

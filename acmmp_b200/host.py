@@ -54,6 +54,11 @@ class ACMMP:
     def SetCompatMode(self, mode):
         _check(self._ctx, self._lib.acmmp_set_compat_mode(self._ctx, int(mode)), "SetCompatMode")
 
+    def SetWaveEmulation(self, resident_blocks):
+        """parity mode: run each half-sweep as the reference launch's block waves (148 resident blocks on a B200;
+        0 = off, the deterministic default).  include/acmmp_b200.h: acmmp_set_wave_emulation."""
+        _check(self._ctx, self._lib.acmmp_set_wave_emulation(self._ctx, int(resident_blocks)), "SetWaveEmulation")
+
     def SetTextureFormat(self, fmt):
         """L.TEX_R32F (default) or L.TEX_AUTO: R8 texels for the next problems whose images all hold
         integer grey levels (bit-identical samples, a quarter of the texture footprint)."""
@@ -128,6 +133,11 @@ class ACMMP:
 
     def run_sweep(self, it, color):
         _check(self._ctx, self._lib.acmmp_run_sweep(self._ctx, int(it), int(color)), "run_sweep")
+
+    def run_sweep_snapshot(self, it, color, snap_planes, snap_costs):
+        """diagnostics: neighbour reads from the given snapshot, own pixel from the live state (in place)."""
+        sp, sc = L.f32(snap_planes), L.f32(snap_costs)
+        _check(self._ctx, self._lib.acmmp_run_sweep_snapshot(self._ctx, int(it), int(color), L.fptr(sp), L.fptr(sc)), "run_sweep_snapshot")
 
     def run_tail(self):
         _check(self._ctx, self._lib.acmmp_run_tail(self._ctx), "run_tail")
@@ -308,7 +318,7 @@ class Scan:
     stage with (device pointer, floats per rank segment) so that a multi-GPU caller
     can all-gather the depth maps (no-op on one GPU)."""
 
-    def __init__(self, cams, pairs, device=0, rank=0, world=1, sequential_geom=False, tex_format=None):
+    def __init__(self, cams, pairs, device=0, rank=0, world=1, sequential_geom=None, tex_format=None):
         self._lib = L.load()
         self._s = C.c_void_p()
         n = len(cams)
@@ -323,7 +333,10 @@ class Scan:
             raise L.AcmmpError(f"acmmp_scan_create failed ({rc}): {self._lib.acmmp_last_error(None).decode()}")
         self.n, self.rank, self.world = n, rank, world
         self._ck(self._lib.acmmp_scan_set_shard(self._s, rank, world), "set_shard")
-        self._ck(self._lib.acmmp_scan_set_sequential_geom(self._s, int(sequential_geom)), "set_sequential_geom")
+        # None: the library's default = the reference's in-place (Gauss-Seidel) geom-1 order on an unsharded scan,
+        # Jacobi on a sharded one; True / False force either
+        if sequential_geom is not None:
+            self._ck(self._lib.acmmp_scan_set_sequential_geom(self._s, int(bool(sequential_geom))), "set_sequential_geom")
         if tex_format is not None:   # default of the library: L.TEX_AUTO
             self._ck(self._lib.acmmp_scan_set_texture_format(self._s, int(tex_format)), "set_texture_format")
 

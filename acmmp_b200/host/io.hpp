@@ -5,6 +5,7 @@
 // StoreColorPlyFileBinaryPointCloud (ACMMP.cpp:382-435).
 #pragma once
 #include <cfloat>
+#include <cmath>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -86,11 +87,14 @@ inline int writeDmb(const std::string &file_path, const float *data, int h, int 
     fclose(f);
     return 0;
 }
-inline int readDmb(const std::string &file_path, Map<float> &out) {
+// the header is not trusted: a map is at most 2^15 x 2^15 with 1 or 3 channels (ACMMP.cpp:263-347 reads
+// whatever the header says); `want_channels` > 0 additionally fixes the channel count
+inline int readDmb(const std::string &file_path, Map<float> &out, int want_channels = 0) {
     FILE *f = fopen(file_path.c_str(), "rb");
     if (!f) return -1;
     int32_t hdr[4] = {-1, 0, 0, 0};
-    if (fread(hdr, sizeof(int32_t), 4, f) != 4 || hdr[0] != 1) {
+    if (fread(hdr, sizeof(int32_t), 4, f) != 4 || hdr[0] != 1 || hdr[1] <= 0 || hdr[2] <= 0 || hdr[1] > 32768 || hdr[2] > 32768 ||
+        (hdr[3] != 1 && hdr[3] != 3) || (want_channels > 0 && hdr[3] != want_channels)) {
         fclose(f);
         return -1;
     }
@@ -101,8 +105,8 @@ inline int readDmb(const std::string &file_path, Map<float> &out) {
 }
 inline int writeDepthDmb(const std::string &p, const Map<float> &depth) { return writeDmb(p, depth.data.data(), depth.rows, depth.cols, 1); }
 inline int writeNormalDmb(const std::string &p, const Map<float> &normal) { return writeDmb(p, normal.data.data(), normal.rows, normal.cols, 3); }
-inline int readDepthDmb(const std::string &p, Map<float> &depth) { return readDmb(p, depth); }
-inline int readNormalDmb(const std::string &p, Map<float> &normal) { return readDmb(p, normal); }
+inline int readDepthDmb(const std::string &p, Map<float> &depth) { return readDmb(p, depth, 1); }
+inline int readNormalDmb(const std::string &p, Map<float> &normal) { return readDmb(p, normal, 3); }
 
 #ifdef ACMMP_IO_WITH_PNG
 // PNG (8 / 16 bit; grey, grey + alpha, RGB, RGBA; not interlaced, no palette) decoded with zlib into
@@ -240,6 +244,68 @@ inline bool ReadImage(const std::string &path, Map<uint8_t> &out, std::string *e
     fclose(f);
     if (!ok && err && err->empty()) *err = path + ": truncated image";
     return ok;
+}
+
+// cv::resize(src, dst, Size(dw, dh), 0, 0, INTER_LINEAR) on 8-bit images, as RunFusion applies it to the colour
+// image (RescaleImageAndCamera, ACMMP.cpp:179-203) and to the mask (acmmp_definitions.cpp:897) when their size
+// differs from the depth map's.  OpenCV's integer scheme: 11-bit coefficients saturate_cast<short>(w * 2048),
+// horizontal pass in int, vertical pass ((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2; an exact
+// 2 x 2 reduction takes the INTER_AREA fast path (a + b + c + d + 2) >> 2 instead (imgproc/resize.cpp).
+inline Map<uint8_t> ResizeLinear8(const Map<uint8_t> &src, int dw, int dh) {
+    const int cn = src.channels, sw = src.cols, sh = src.rows;
+    Map<uint8_t> dst(dh, dw, cn);
+    if (sw == dw && sh == dh) {
+        dst.data = src.data;
+        return dst;
+    }
+    if (sw == 2 * dw && sh == 2 * dh) {
+        for (int y = 0; y < dh; ++y)
+            for (int x = 0; x < dw; ++x)
+                for (int k = 0; k < cn; ++k)
+                    dst.at(y, x, k) = (uint8_t)((src.at(2 * y, 2 * x, k) + src.at(2 * y, 2 * x + 1, k) + src.at(2 * y + 1, 2 * x, k) +
+                                                 src.at(2 * y + 1, 2 * x + 1, k) + 2) >> 2);
+        return dst;
+    }
+    const double scale_x = (double)sw / dw, scale_y = (double)sh / dh;
+    auto coef = [](float f) {   // saturate_cast<short>(f * INTER_RESIZE_COEF_SCALE): round half to even
+        const long v = lrintf(f * 2048.0f);
+        return (int)(v < -32768 ? -32768 : v > 32767 ? 32767 : v);
+    };
+    std::vector<int> xofs(dw), yofs(dh), alpha(2 * (size_t)dw), beta(2 * (size_t)dh);
+    for (int dx = 0; dx < dw; ++dx) {
+        float fx = (float)((dx + 0.5) * scale_x - 0.5);
+        int sx = (int)floorf(fx);
+        fx -= sx;
+        if (sx < 0) { fx = 0; sx = 0; }
+        if (sx >= sw - 1) { fx = 0; sx = sw - 1; }
+        xofs[dx] = sx;
+        alpha[2 * dx] = coef(1.f - fx);
+        alpha[2 * dx + 1] = coef(fx);
+    }
+    for (int dy = 0; dy < dh; ++dy) {
+        float fy = (float)((dy + 0.5) * scale_y - 0.5);
+        int sy = (int)floorf(fy);
+        fy -= sy;
+        yofs[dy] = sy;
+        beta[2 * dy] = coef(1.f - fy);
+        beta[2 * dy + 1] = coef(fy);
+    }
+    std::vector<int> row0((size_t)dw * cn), row1((size_t)dw * cn);
+    auto hpass = [&](int sy, std::vector<int> &row) {
+        sy = sy < 0 ? 0 : (sy > sh - 1 ? sh - 1 : sy);
+        for (int dx = 0; dx < dw; ++dx) {
+            const int sx = xofs[dx], sx1 = sx + 1 < sw ? sx + 1 : sw - 1;
+            for (int k = 0; k < cn; ++k) row[(size_t)dx * cn + k] = src.at(sy, sx, k) * alpha[2 * dx] + src.at(sy, sx1, k) * alpha[2 * dx + 1];
+        }
+    };
+    for (int dy = 0; dy < dh; ++dy) {
+        hpass(yofs[dy], row0);
+        hpass(yofs[dy] + 1, row1);
+        const int b0 = beta[2 * dy], b1 = beta[2 * dy + 1];
+        for (size_t i = 0; i < (size_t)dw * cn; ++i)
+            dst.data[(size_t)dy * dw * cn + i] = (uint8_t)((((b0 * (row0[i] >> 4)) >> 16) + ((b1 * (row1[i] >> 4)) >> 16) + 2) >> 2);
+    }
+    return dst;
 }
 
 // grey float image as cv::imread(IMREAD_GRAYSCALE) + convertTo(CV_32FC1) gives it (ACMMP.cpp:534-541):

@@ -53,10 +53,10 @@ assert C.sizeof(Camera) == 100
 EXPORTS = [
     "acmmp_create", "acmmp_destroy", "acmmp_last_error", "acmmp_version", "acmmp_default_params",
     "acmmp_set_geom_consistency", "acmmp_set_hierarchy", "acmmp_set_planar_prior_params",
-    "acmmp_set_compat_mode", "acmmp_set_texture_format", "acmmp_texture_is_u8", "acmmp_get_params", "acmmp_set_problem", "acmmp_set_depth_map",
+    "acmmp_set_compat_mode", "acmmp_set_wave_emulation", "acmmp_set_texture_format", "acmmp_texture_is_u8", "acmmp_get_params", "acmmp_set_problem", "acmmp_set_depth_map",
     "acmmp_set_warm_start", "acmmp_set_hierarchy_inputs", "acmmp_set_seeded_planes",
     "acmmp_set_planar_prior", "acmmp_build_planar_prior", "acmmp_run", "acmmp_run_init",
-    "acmmp_run_sweep", "acmmp_run_tail", "acmmp_get_result", "acmmp_get_maps",
+    "acmmp_run_sweep", "acmmp_run_sweep_snapshot", "acmmp_run_tail", "acmmp_get_result", "acmmp_get_maps",
     "acmmp_get_depth_device", "acmmp_get_state", "acmmp_set_state", "acmmp_width", "acmmp_height",
     "acmmp_sync", "acmmp_launch_count", "acmmp_last_timing", "acmmp_jbu_depth", "acmmp_resize_linear",
     "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_measure_tex_peak", "acmmp_measure_tex_peak_u8", "acmmp_tex_sample", "acmmp_tex_sample_u8", "acmmp_get_planar_prior", "acmmp_delaunay", "acmmp_set_delaunay_threads", "acmmp_timing_collect",
@@ -101,6 +101,7 @@ def load():
     lib.acmmp_set_hierarchy.argtypes = [vp]
     lib.acmmp_set_planar_prior_params.argtypes = [vp]
     lib.acmmp_set_compat_mode.argtypes = [vp, C.c_int]
+    lib.acmmp_set_wave_emulation.argtypes = [vp, C.c_int]
     lib.acmmp_set_texture_format.argtypes = [vp, C.c_int]
     lib.acmmp_texture_is_u8.argtypes = [vp]
     lib.acmmp_get_params.argtypes = [vp, C.POINTER(Params)]
@@ -117,6 +118,7 @@ def load():
     lib.acmmp_run.argtypes = [vp, C.c_uint64]
     lib.acmmp_run_init.argtypes = [vp, C.c_uint64]
     lib.acmmp_run_sweep.argtypes = [vp, C.c_int, C.c_int]
+    lib.acmmp_run_sweep_snapshot.argtypes = [vp, C.c_int, C.c_int, fp, fp]
     lib.acmmp_run_tail.argtypes = [vp]
     lib.acmmp_get_result.argtypes = [vp, fp, fp, up]
     lib.acmmp_get_maps.argtypes = [vp, fp, fp, fp]

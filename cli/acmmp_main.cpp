@@ -39,6 +39,30 @@ static bool find_image(const std::string &folder, int id, Map<uint8_t> &im, std:
     return false;
 }
 
+// <dense>/<mask_dir>/%08d.png as cv::imread(path, -1) returns it (acmmp_definitions.cpp:886-895), first channel, as bytes;
+// 16-bit samples are clamped to 255 (only `< 128` is asked of them).  PGM / raw containers are accepted too.
+static bool find_mask(const std::string &folder, int id, Map<uint8_t> &m, std::string &err, int device) {
+    Map<uint16_t> png;
+    std::string e;
+    if (ReadPng16(folder + "/" + id_name(id, ".png"), png, nullptr, &e)) {
+        m = Map<uint8_t>(png.rows, png.cols, 1);
+        for (size_t k = 0; k < (size_t)png.rows * png.cols; ++k) {
+            const uint16_t v = png.data[k * png.channels];
+            m.data[k] = (uint8_t)(v > 255 ? 255 : v);
+        }
+        return true;
+    }
+    if (e.find("cannot open") == std::string::npos) {
+        err = e;
+        return false;
+    }
+    Map<uint8_t> any;
+    if (!find_image(folder, id, any, err, false, device)) return false;
+    m = Map<uint8_t>(any.rows, any.cols, 1);
+    for (size_t k = 0; k < (size_t)any.rows * any.cols; ++k) m.data[k] = any.data[k * any.channels];
+    return true;
+}
+
 int main(int argc, char **argv) {
     std::string dense_folder, output_dir = "/ACMMP", mask_dir = " ", image_dir = "/images";
     float consistency_scalar = 0.3f;
@@ -191,25 +215,24 @@ int main(int argc, char **argv) {
                         return EXIT_FAILURE;
                     }
                 }
-                if (color.cols != cams_out[i].width || color.rows != cams_out[i].height) {
-                    fprintf(stderr, "image %d: colour image size differs from the depth map (resize not built in)\n", problems[i].ref_image_id);
-                    return EXIT_FAILURE;
-                }
                 if (color.channels == 1) {   // grey input: replicate like imread(IMREAD_COLOR)
                     Map<uint8_t> c3(color.rows, color.cols, 3);
                     for (size_t k = 0; k < (size_t)color.rows * color.cols; ++k) c3.data[3 * k] = c3.data[3 * k + 1] = c3.data[3 * k + 2] = color.data[k];
                     color = c3;
                 }
+                // RescaleImageAndCamera (ACMMP.cpp:179-203): the colour image at the size of the depth map
+                if (color.cols != cams_out[i].width || color.rows != cams_out[i].height) color = ResizeLinear8(color, cams_out[i].width, cams_out[i].height);
                 std::vector<uint8_t> mask;
-                if (mask_dir != " ") {   // acmmp_definitions.cpp:870-895: mask = png < 128
+                if (mask_dir != " ") {   // acmmp_definitions.cpp:884-899: %08d.png, resized to the depth map, mask = value < 128
                     Map<uint8_t> m;
                     std::string err;
-                    if (!find_image(dense_folder + "/" + mask_dir, problems[i].ref_image_id, m, err, false, device) || m.cols != cams_out[i].width || m.rows != cams_out[i].height) {
-                        fprintf(stderr, "mask of image %d missing or of the wrong size\n", problems[i].ref_image_id);
+                    if (!find_mask(dense_folder + "/" + mask_dir, problems[i].ref_image_id, m, err, device)) {
+                        fprintf(stderr, "mask of image %d: %s\n", problems[i].ref_image_id, err.c_str());
                         return EXIT_FAILURE;
                     }
+                    if (m.cols != cams_out[i].width || m.rows != cams_out[i].height) m = ResizeLinear8(m, cams_out[i].width, cams_out[i].height);
                     mask.resize((size_t)m.rows * m.cols);
-                    for (size_t k = 0; k < mask.size(); ++k) mask[k] = m.data[k * m.channels] < 128 ? 1 : 0;
+                    for (size_t k = 0; k < mask.size(); ++k) mask[k] = m.data[k] < 128 ? 1 : 0;
                 }
                 // colour and mask come from the host, so the maps take the same way (one flag per call)
                 Map<float> hd, hn;

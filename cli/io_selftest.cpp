@@ -1,6 +1,8 @@
 // io_selftest.cpp - exercises acmmp_b200/host/io.hpp from the CPU test-suite (tests/test_host_io.py):
 //   io_selftest <dir>   reads <dir>/pair.txt, <dir>/cams/00000000_cam.txt, <dir>/in.dmb, <dir>/img.ppm, <dir>/points.bin
 //   io_selftest --png in.png out.bin   decodes a PNG (ReadPng16) and dumps the samples
+//   io_selftest --resize8 in.ppm out.bin W H   cv::resize(INTER_LINEAR) of an 8-bit image (ResizeLinear8)
+//   io_selftest --dmb file depth|normal|any    header validation of the .dmb readers
 //                       writes <dir>/out.dmb, <dir>/gray.dmb, <dir>/out.ply and prints what it parsed as key=value lines
 #include <cstdio>
 #include <cstdlib>
@@ -28,6 +30,28 @@ int main(int argc, char **argv) {
         fwrite(png.data.data(), sizeof(uint16_t), png.data.size(), o);
         fclose(o);
         return 0;
+    }
+    if (argc >= 6 && std::string(argv[1]) == "--resize8") {   // io_selftest --resize8 in.ppm|pgm out.bin W H: ResizeLinear8
+        Map<uint8_t> im;
+        std::string err;
+        if (!ReadImage(argv[2], im, &err)) {
+            fprintf(stderr, "%s\n", err.c_str());
+            return 14;
+        }
+        const Map<uint8_t> out = ResizeLinear8(im, atoi(argv[4]), atoi(argv[5]));
+        FILE *o = fopen(argv[3], "wb");
+        if (!o) return 13;
+        fwrite(out.data.data(), 1, out.data.size(), o);
+        fclose(o);
+        printf("resized=%d,%d,%d\n", out.rows, out.cols, out.channels);
+        return 0;
+    }
+    if (argc >= 4 && std::string(argv[1]) == "--dmb") {   // io_selftest --dmb file depth|normal|any: 0 if accepted
+        Map<float> m;
+        const std::string kind = argv[3];
+        const int rc = kind == "depth" ? readDepthDmb(argv[2], m) : kind == "normal" ? readNormalDmb(argv[2], m) : readDmb(argv[2], m);
+        printf("dmb_rc=%d\n", rc);
+        return rc ? 15 : 0;
     }
     const std::string dir = argv[1];
     std::vector<Problem> problems;

@@ -121,6 +121,17 @@ int acmmp_set_geom_consistency(acmmp_ctx *ctx, int multi_geometry);
 int acmmp_set_hierarchy(acmmp_ctx *ctx);
 int acmmp_set_planar_prior_params(acmmp_ctx *ctx);
 int acmmp_set_compat_mode(acmmp_ctx *ctx, int mode);
+/* Emulation of the reference launch's block waves (0 = off, the default: every same-colour read sees the
+ * state before the half-sweep - deterministic, independent of the GPU).  Black/RedPixelUpdate read
+ * same-colour neighbours that other blocks of the same launch rewrite (ACMMP.cu:895-988 vs :1165-1171).
+ * The reference launches 32 x 32-pixel blocks (32 x 16 threads, ACMMP.cu:1415-1424) of which
+ * `resident_blocks` fit on the GPU at a time (B200: 148 = one 512-thread, 128-register block per SM);
+ * blocks of a later wave start when the earlier wave has stored its results, so the top 4 rows of such a
+ * block see NEW planes / costs above them.  With resident_blocks > 0 a half-sweep runs as one sub-launch
+ * per wave that reproduces this (tools/parity_study.py, profiles/r2*_parity_study.json: 99.5 % of the
+ * pixels where the product differs from the reference build sit in those 4 rows).  Parity / diagnosis
+ * mode: same work, a few more launches. */
+int acmmp_set_wave_emulation(acmmp_ctx *ctx, int resident_blocks);
 /* acmmp_tex_format for the following acmmp_set_problem calls (default ACMMP_TEX_R32F);
  * acmmp_texture_is_u8: 1 when the current problem's views sit in R8 texels. */
 int acmmp_set_texture_format(acmmp_ctx *ctx, int format);
@@ -196,6 +207,13 @@ int acmmp_run(acmmp_ctx *ctx, uint64_t seed);
 int acmmp_run_init(acmmp_ctx *ctx, uint64_t seed);        /* RandomInitialization */
 int acmmp_run_sweep(acmmp_ctx *ctx, int iter, int color); /* 0 = black, 1 = red  */
 int acmmp_run_tail(acmmp_ctx *ctx); /* GetDepthandNormal + Black/RedPixelFilter */
+/* Diagnostics: one half-sweep whose NEIGHBOUR reads (the candidates of the 8 arms) come from the
+ * given host snapshot (planes 4 f32, cost) while the pixel's own plane is the context's state, which
+ * is updated in place.  Black/RedPixelUpdate read same-colour neighbours while other threads rewrite
+ * them (ACMMP.cu:895-988 vs :1092,1165-1171): a reference pixel has seen the state before the launch,
+ * the state after it, or a mix.  Feeding the reference's OUTPUT as the snapshot bounds the second
+ * case; tools/parity_study.py uses it to attribute differences to that race. */
+int acmmp_run_sweep_snapshot(acmmp_ctx *ctx, int iter, int color, const float *snap_planes4, const float *snap_cost);
 
 /* ---- outputs ---------------------------------------------------------------
  * ACMMP::GetPlaneHypothesis / GetCost (ACMMP.cpp:848-856): planes4 is
@@ -318,9 +336,11 @@ int acmmp_scan_set_shard(acmmp_scan *s, int rank, int world);
  * acmmp_scan_level_is_u8: what the current level uses. */
 int acmmp_scan_set_texture_format(acmmp_scan *s, int format);
 int acmmp_scan_level_is_u8(const acmmp_scan *s);
-/* 0 = Jacobi (default; geom-1 reads the geom-0 maps of all views), 1 = the
- * reference's in-place order dependence (geom-1 reads what earlier views of the
- * same loop already wrote; only meaningful with world == 1). */
+/* Order of the second geometric-consistency pass.  1 = the reference's in-place
+ * order dependence (ProcessProblem rewrites depths_geom.dmb, so geom-1 of view i reads
+ * what earlier views of the same loop already wrote; ACMMP.cpp:608-635) - only
+ * meaningful with world == 1.  0 = Jacobi (geom-1 reads the geom-0 maps of all
+ * views).  -1 = default: 1 on an unsharded scan, 0 on a sharded one. */
 int acmmp_scan_set_sequential_geom(acmmp_scan *s, int on);
 int acmmp_scan_num_levels(const acmmp_scan *s);
 /* builds the image pyramid level (InputInitialization's resize,

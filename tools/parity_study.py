@@ -1,0 +1,259 @@
+#!/usr/bin/env python
+"""Where do the product's half-sweeps differ from the reference build's, and why?
+
+The reference's Black/RedPixelUpdate read same-colour neighbours while other threads of the same launch
+rewrite them (ACMMP.cu:895-988 vs :1092,1165-1171), so one reference half-sweep from state S is not a
+function of S: a same-colour candidate carries either its value in S ("old") or its value in the
+launch's output R ("new").  The product always serves "old".  For every half-sweep this tool runs, from
+the reference's own state S:
+
+  R, R2   the reference kernel twice                      -> its self-agreement
+  M_old   the product                                     -> what ships
+  M_new   the product with R injected as the neighbour snapshot (acmmp_run_sweep_snapshot)
+
+and classifies every interior pixel of the colour: equal(M_old, R); else equal(M_new, R) = explained by
+the race (the reference saw finished neighbours); else unexplained (a mix of old and new reads, or a
+real difference).  Unexplained pixels are histogrammed by row / column modulo the reference's block
+(32 x 32 pixels: 32 x 16 threads, one colour), by distance to the border and, in planar-prior runs, by
+prior coverage.  Then full runs: reference twice, product once: depth <= 0.1 % / normal <= 0.5 deg.
+
+Writes profiles-ready JSON to gpurun_out/parity_study_<tag>.json and, with --dump, the arrays of the
+first half-sweeps to gpurun_out/parity_dump_<tag>.npz for offline analysis."""
+import argparse
+import json
+import os
+import sys
+import time
+import traceback
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+from acmmp_b200 import host  # noqa: E402
+from acmmp_b200.scene import make_scene  # noqa: E402
+import refbind  # noqa: E402
+from gpu_parity import bits, color_mask, interior, gt_planes, problem, depth_normal_tol, plane_stats  # noqa: E402
+
+
+def ref_set_state(ref, st):
+    ref.set_planes(0, st[0])
+    ref.set_scalars(0, st[1])
+    ref.set_scalars(2, st[2])
+    ref.set_rng(st[3])
+
+
+def border_dist(h, w):
+    yy, xx = np.mgrid[0:h, 0:w]
+    return np.minimum(np.minimum(yy, h - 1 - yy), np.minimum(xx, w - 1 - xx))
+
+
+def half_sweeps(ref, mine, h, w, masks=None, dump=None, dump_key=""):
+    res = {}
+    bd = border_dist(h, w)
+    for it in (0, 1):
+        for color in (0, 1):
+            S = ref.get_state()[:4]
+            ref.run_sweep(it, color)
+            R = ref.get_state()[:4]
+            ref_set_state(ref, S)
+            ref.run_sweep(it, color)
+            R2 = ref.get_state()[:4]
+            mine.set_state(*S)
+            mine.run_sweep(it, color)
+            Mo = mine.get_state()
+            mine.set_state(*S)
+            mine.run_sweep_snapshot(it, color, R[0], R[1])
+            Mn = mine.get_state()
+            cm = color_mask(h, w, color)
+            inner = cm & interior(h, w, 4)
+            eq_old = (bits(Mo[0]) == bits(R[0])).all(-1)
+            eq_new = (bits(Mn[0]) == bits(R[0])).all(-1)
+            eq_self = (bits(R2[0]) == bits(R[0])).all(-1)
+            unexpl = inner & ~eq_old & ~eq_new
+            ys, xs = np.nonzero(unexpl)
+            n = int(inner.sum())
+            r = {
+                "pixels": n,
+                "equal_old": float(eq_old[inner].mean()),
+                "explained_by_new_reads": float((~eq_old & eq_new)[inner].mean()),
+                "unexplained": float(unexpl[inner].mean()),
+                "ref_rerun_equal": float(eq_self[inner].mean()),
+                # pixels where the reference agrees with itself yet not with either product variant
+                "unexplained_where_ref_is_stable": float((unexpl & eq_self)[inner].mean()),
+                "rng_equal_old": float((Mo[3] == R[3]).all(-1)[inner].mean()),
+                "interior32": {"equal_old": float(eq_old[cm & interior(h, w, 32)].mean()),
+                               "unexplained": float(unexpl[cm & interior(h, w, 32)].mean()),
+                               "ref_rerun_equal": float(eq_self[cm & interior(h, w, 32)].mean())},
+                "unexplained_y_mod32": np.bincount(ys % 32, minlength=32).tolist(),
+                "unexplained_x_mod32": np.bincount(xs % 32, minlength=32).tolist(),
+                "old_differs_y_mod32": np.bincount(np.nonzero(inner & ~eq_old)[0] % 32, minlength=32).tolist(),
+                "unexplained_border_dist": np.bincount(np.minimum(bd[unexpl], 31), minlength=32).tolist(),
+                "unexplained_cost_equal": float((bits(Mo[1]) == bits(R[1]))[unexpl].mean()) if unexpl.any() else 1.0,
+            }
+            if masks is not None:
+                for name, mk in (("covered", masks > 0), ("uncovered", masks == 0)):
+                    sel = inner & mk
+                    r[name] = {"pixels": int(sel.sum()), "equal_old": float(eq_old[sel].mean()), "explained_by_new_reads": float((~eq_old & eq_new)[sel].mean()),
+                               "unexplained": float(unexpl[sel].mean()), "ref_rerun_equal": float(eq_self[sel].mean())}
+            res[f"it{it}_c{color}"] = r
+            if dump is not None and it == 0:
+                k = f"{dump_key}_c{color}_"
+                dump.update({k + "S_planes": S[0], k + "S_costs": S[1], k + "S_sel": S[2], k + "R_planes": R[0], k + "R_costs": R[1],
+                             k + "R_sel": R[2], k + "R2_planes": R2[0], k + "Mo_planes": Mo[0], k + "Mo_costs": Mo[1], k + "Mn_planes": Mn[0],
+                             k + "S_rng": S[3], k + "R_rng": R[3]})
+            ref_set_state(ref, R)
+    return res
+
+
+def study(scene, view, seed, dump=None):
+    h, w = scene["height"], scene["width"]
+    images, cams, ids = problem(scene, view)
+    depths = [scene["depths"][i] for i in ids]
+    sc_np = scene
+    rs = np.random.default_rng(0)
+    out = {"size": [w, h], "sources": len(ids) - 1}
+    ref = refbind.RefACMMP(0)
+    ref.set_problem(images, cams)
+
+    # fixed-hypothesis initial cost + view masks (north_star: NCC <= 1e-4, masks bit-exact)
+    pl = gt_planes(sc_np, view, rs, 0.02)
+    ref.set_flags(seeded=1)
+    ref.set_planes(2, pl)
+    ref.run_init(seed)
+    r0 = ref.get_state()
+    m = host.ACMMP(0)
+    m.InputInitialization(images, cams)
+    m.SetPlanarPrior(pl)
+    m.run_init(seed)
+    m0 = m.get_state()
+    out["fixed_hypothesis_init"] = {"cost_bit_equal": float((bits(m0[1]) == bits(r0[1])).mean()), "cost_max_abs": float(np.abs(m0[1] - r0[1]).max()),
+                                    "masks_equal": float((m0[2] == r0[2]).mean())}
+    m.close()
+
+    # photometric
+    ref.set_flags(seeded=0, geom=0, planar_prior=0, hierarchy=0, upsample=0)
+    ref.run_init(seed)
+    m = host.ACMMP(0)
+    m.InputInitialization(images, cams)
+    m.run_init(seed)
+    out["random_init_bit_equal"] = plane_stats(m.get_state()[0], ref.get_state()[0])
+    out["photometric"] = half_sweeps(ref, m, h, w, dump=dump, dump_key="photo")
+    ref.run_tail()
+    rp, rc_ = ref.get_state()[:2]
+    m.close()
+
+    # geometric consistency, warm start = the reference's photometric result
+    depth, normal, cost = rp[..., 3].copy(), rp[..., :3].copy(), rc_.copy()
+    dmaps = [depth] + depths[1:]
+    ref.set_flags(geom=1, seeded=0, planar_prior=0, hierarchy=0, upsample=0)
+    for i, d in enumerate(dmaps):
+        ref.set_depth_map(i, d)
+    ref.set_planes(0, rp)
+    ref.set_scalars(0, cost)
+    m = host.ACMMP(0)
+    m.SetGeomConsistencyParams(False)
+    m.InputInitialization(images, cams, depths=dmaps)
+    m.CudaSpaceInitialization(warm_start=(depth, normal, cost))
+    ref.run_init(seed)
+    m.run_init(seed)
+    out["geom_init_bit_equal"] = plane_stats(m.get_state()[0], ref.get_state()[0])
+    out["geom"] = half_sweeps(ref, m, h, w, dump=dump, dump_key="geom")
+    m.close()
+
+    # planar prior (supplied prior: noisy ground-truth planes, 10 % holes, uncovered frame)
+    pl = gt_planes(sc_np, view, rs, 0.01)
+    masks = np.zeros((h, w), np.uint32)
+    masks[h // 6: 5 * h // 6, w // 6: 5 * w // 6] = 1
+    masks[(rs.random((h, w)) < 0.1)] = 0
+    ref.set_flags(geom=0, seeded=0, planar_prior=1, hierarchy=0, upsample=0)
+    ref.set_planes(1, pl)
+    ref.set_scalars(3, masks)
+    ref.run_init(seed)
+    m = host.ACMMP(0)
+    m.SetPlanarPriorParams()
+    m.InputInitialization(images, cams)
+    m.CudaPlanarPriorInitialization(pl, masks)
+    m.run_init(seed)
+    out["prior_init_bit_equal"] = plane_stats(m.get_state()[0], ref.get_state()[0])
+    if dump is not None:
+        dump["prior_planes"] = pl
+        dump["prior_masks"] = masks
+    out["prior"] = half_sweeps(ref, m, h, w, masks=masks, dump=dump, dump_key="prior")
+    m.close()
+
+    # full runs: reference twice, product once
+    full = {}
+    for mode in ("photometric", "prior"):
+        ref.set_flags(geom=0, seeded=0, planar_prior=int(mode == "prior"), hierarchy=0, upsample=0)
+        ms_a = ref.run(seed)
+        ra = ref.get_state()[0]
+        ms_b = ref.run(seed)
+        rb = ref.get_state()[0]
+        m = host.ACMMP(0)
+        if mode == "prior":
+            m.SetPlanarPriorParams()
+        m.InputInitialization(images, cams)
+        if mode == "prior":
+            m.CudaPlanarPriorInitialization(pl, masks)
+        m.RunPatchMatch(seed)
+        m.RunPatchMatch(seed)
+        tm = m.last_timing()
+        mp = m.get_state()[0]
+        m.close()
+        r = {"ref_ms": [ms_a, ms_b], "ours_ms": tm}
+        for b in (8, 32):
+            inner = interior(h, w, b)
+            r[f"interior{b}"] = {"ours_vs_ref": {"plane_bit_equal": plane_stats(mp, ra, inner), **depth_normal_tol(mp, ra, inner)},
+                                 "ref_vs_ref": {"plane_bit_equal": plane_stats(ra, rb, inner), **depth_normal_tol(ra, rb, inner)}}
+        gt = depths[0]
+        inner = interior(h, w, 8)
+        r["depth_within_1pct_of_truth"] = {"ours": float((np.abs(mp[..., 3] - gt) / gt < 0.01)[inner].mean()),
+                                           "ref": float((np.abs(ra[..., 3] - gt) / gt < 0.01)[inner].mean())}
+        full[mode] = r
+    out["full_run"] = full
+    ref.close()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--tag", default="r2")
+    ap.add_argument("--configs", default="320x240x5x4,640x480x5x4,1600x1200x11x10")
+    ap.add_argument("--dump", default="320x240x5x4", help="config whose first half-sweeps are dumped (npz)")
+    ap.add_argument("--seed", type=int, default=1234)
+    args = ap.parse_args()
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    report = {}
+    for cfg in args.configs.split(","):
+        w, h, nv, ns = [int(x) for x in cfg.split("x")]
+        t0 = time.time()
+        try:
+            if w >= 1600:
+                sc = make_scene(nv, w, h, ns, seed=1, span_deg=(10.0, 8.0), device="cuda")
+                view = nv // 2
+            else:
+                sc = make_scene(nv, w, h, ns, seed=0)
+                view = 0
+            dump = {} if cfg == args.dump else None
+            report[cfg] = study(sc, view, args.seed, dump)
+            if dump:
+                np.savez_compressed(os.path.join(ROOT, "gpurun_out", f"parity_dump_{args.tag}.npz"), **dump)
+        except Exception as e:
+            report[cfg] = {"error": repr(e), "trace": traceback.format_exc()[-2000:]}
+        report[cfg]["seconds"] = round(time.time() - t0, 1)
+        with open(os.path.join(ROOT, "gpurun_out", f"parity_study_{args.tag}.json"), "w") as f:
+            json.dump(report, f, indent=1)
+        short = {k: v for k, v in report[cfg].items() if k in ("fixed_hypothesis_init", "full_run", "error", "trace", "seconds")}
+        print(cfg, json.dumps(short), flush=True)
+        for mode in ("photometric", "geom", "prior"):
+            for k, r in report[cfg].get(mode, {}).items():
+                print(f"  {mode} {k}: old {r['equal_old']:.4f} +new {r['explained_by_new_reads']:.4f} unexplained {r['unexplained']:.4f} "
+                      f"(ref stable there {r['unexplained_where_ref_is_stable']:.4f}) ref-rerun {r['ref_rerun_equal']:.4f}", flush=True)
+
+
+if __name__ == "__main__":
+    main()
