@@ -207,3 +207,42 @@ def test_cli_seeded_mode_reads_prior_pngs(cli_run):
     sh.rmtree(os.path.join(dense, "priors"))
     out = subprocess.run([EXE, dense, "-p", "--no_fusion"], capture_output=True, text=True)
     assert out.returncode != 0 and "no suitable priors" in out.stderr
+
+
+def test_cli_reads_png_masks_in_the_reference_format(cli_run):
+    """--mask_dir: <dense>/<mask_dir>/%08d.png read like cv::imread(-1), resized to the depth map with
+    cv::resize(INTER_LINEAR) and thresholded `< 128` (acmmp_definitions.cpp:884-899).  The masks are written at
+    twice the depth-map size, so the CLI's own 8-bit resize (io.hpp ResizeLinear8) is on the path; the expected
+    cloud comes from the device fusion fed with masks that cv2 made from the same files."""
+    cv2 = pytest.importorskip("cv2")
+    from acmmp_b200 import host
+    sc, dense, ids, _ = cli_run
+    n = len(ids)
+    rng = np.random.default_rng(3)
+    os.makedirs(os.path.join(dense, "masks"), exist_ok=True)
+    masks = []
+    for i in range(n):
+        big = cv2.GaussianBlur((rng.random((480, 640)) * 255).astype(np.uint8), (0, 0), 9)
+        big = cv2.normalize(big, None, 0, 255, cv2.NORM_MINMAX)
+        assert cv2.imwrite(os.path.join(dense, "masks", "%08d.png" % ids[i]), big)
+        back = cv2.imread(os.path.join(dense, "masks", "%08d.png" % ids[i]), -1)
+        masks.append((cv2.resize(back, (320, 240)) < 128).astype(np.uint8))
+        assert 0.2 < masks[-1].mean() < 0.8
+    out = subprocess.run([EXE, dense, "--seed", "5", "--output_dir", "/MASKED", "--mask_dir", "masks"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    xyz_n, col = read_ply(os.path.join(dense, "MASKED", "ACMMP_model.ply"))
+    depths, normals = [], []
+    for i in range(n):
+        folder = os.path.join(dense, "MASKED", "2333_%08d" % ids[i])
+        depths.append(read_dmb(os.path.join(folder, "depths_geom.dmb")))
+        normals.append(read_dmb(os.path.join(folder, "normals.dmb")))
+    pts, per = host.RunFusion(sc["cams"], sc["pairs"], depths, normals, masks=masks)
+    assert len(pts) == len(xyz_n), (len(pts), len(xyz_n))
+    assert (pts[:, :6].astype(np.float32).view(np.uint32) == xyz_n.view(np.uint32)).all()
+    unmasked, _ = read_ply(os.path.join(dense, "ACMMP", "ours.ply")) if os.path.exists(os.path.join(dense, "ACMMP", "ours.ply")) else (None, None)
+    if unmasked is not None:
+        assert len(xyz_n) < len(unmasked)
+    # a missing mask is an error, not a silent no-mask run
+    os.remove(os.path.join(dense, "masks", "%08d.png" % ids[0]))
+    out = subprocess.run([EXE, dense, "--seed", "5", "--output_dir", "/MASKED", "--mask_dir", "masks"], capture_output=True, text=True)
+    assert out.returncode != 0 and "mask of image" in out.stderr

@@ -170,9 +170,13 @@ def test_planar_prior_half_sweeps_vs_live_reference_kernels():
             rp, mp = ref.get_state()[0], m.get_state()[0]
             inner = interior(h, w, 4) & color_mask(h, w, color)
             same = (gu.bits(mp) == gu.bits(rp)).all(-1)
-            assert same[inner & (masks > 0)].mean() >= 0.85, (it, color, same[inner & (masks > 0)].mean())
-            assert same[inner & (masks == 0)].mean() >= 0.80, (it, color, same[inner & (masks == 0)].mean())
-            assert same[inner].mean() >= 0.85, (it, color, same[inner].mean())
+            # measured on B200 (profiles/r2b_parity_study.json, 320x240): covered 0.884-0.993, uncovered 0.906-0.995, all
+            # 0.923-0.994; the reference against itself 0.960-0.998.  The rest is the reference's intra-launch race on the
+            # adoption re-read: 79 % of the differing covered pixels carry a plane that is two
+            # propagation hops away (tools/prior_race_attribution.py)
+            assert same[inner & (masks > 0)].mean() >= 0.86, (it, color, same[inner & (masks > 0)].mean())
+            assert same[inner & (masks == 0)].mean() >= 0.88, (it, color, same[inner & (masks == 0)].mean())
+            assert same[inner].mean() >= 0.90, (it, color, same[inner].mean())
     m.close()
     ref.close()
 
@@ -272,6 +276,27 @@ def test_full_schedule_recovers_the_scene_and_sharding_is_invisible():
         for k in range(3):
             assert (gu.bits(a[v][k]) == gu.bits(a2[v][k])).all(), ("rerun", v, k)
             assert (gu.bits(a[v][k]) == gu.bits(b[v][k])).all(), ("3 shards", v, k)
+
+
+def test_unsharded_scan_defaults_to_the_reference_in_place_geom_order():
+    """ProcessProblem rewrites depths_geom.dmb in place, so geom-1 of view i reads this pass's maps of the views
+    before it (ACMMP.cpp:608-635).  An unsharded scan does that by default; Jacobi is for sharded scans."""
+    sc = make_scene(5, 320, 240, 4, seed=4)
+    default = run_scan(sc, sequential=None)
+    in_place = run_scan(sc, sequential=True)
+    jacobi = run_scan(sc, sequential=False)
+    differs = False
+    for v in range(5):
+        for k in range(3):
+            assert (gu.bits(default[v][k]) == gu.bits(in_place[v][k])).all(), (v, k)
+            differs |= bool((gu.bits(default[v][k]) != gu.bits(jacobi[v][k])).any())
+    assert differs
+    # view 0 has no earlier view: identical either way
+    assert (gu.bits(default[0][0]) == gu.bits(jacobi[0][0])).all()
+    # a sharded scan runs Jacobi by default
+    sharded = run_scan(sc, world=2, sequential=None)
+    for v in range(5):
+        assert (gu.bits(sharded[v][0]) == gu.bits(jacobi[v][0])).all(), v
 
 
 def test_r8_level_texture_is_invisible():

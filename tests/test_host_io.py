@@ -97,3 +97,42 @@ def test_png_reader_against_cv2(tmp_path):
     bad = str(tmp_path / "bad.png")
     open(bad, "wb").write(b"not a png")
     assert subprocess.run([exe, "--png", bad, str(tmp_path / "x.bin")], capture_output=True).returncode == 12
+
+
+@pytest.mark.parametrize("shape,dst", [((48, 64, 1), (32, 24)), ((48, 64, 3), (32, 24)), ((37, 53, 3), (80, 61)), ((37, 53, 1), (19, 11)),
+                                       ((30, 40, 1), (40, 30)), ((96, 128, 3), (100, 75))])
+def test_resize_linear_8bit_equals_cv2(tmp_path, shape, dst):
+    """ResizeLinear8 (io.hpp) = cv::resize(INTER_LINEAR) on 8-bit images, incl. the 2 x 2 INTER_AREA fast path:
+    what RunFusion applies to colour images and masks whose size differs from the depth map's
+    (ACMMP.cpp:179-203, acmmp_definitions.cpp:897)."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(sum(shape) + dst[0])
+    img = rng.integers(0, 256, size=shape, dtype=np.uint8)
+    path = str(tmp_path / ("in.ppm" if shape[2] == 3 else "in.pgm"))
+    with open(path, "wb") as f:
+        f.write((b"P6" if shape[2] == 3 else b"P5") + b"\n%d %d\n255\n" % (shape[1], shape[0]) + img.tobytes())
+    out = str(tmp_path / "out.bin")
+    r = subprocess.run([EXE, "--resize8", path, out, str(dst[0]), str(dst[1])], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    got = np.fromfile(out, np.uint8).reshape(dst[1], dst[0], shape[2])
+    src = img[..., ::-1] if shape[2] == 3 else img[..., 0]          # the reader keeps BGR in memory
+    want = cv2.resize(np.ascontiguousarray(src), dst, interpolation=cv2.INTER_LINEAR).reshape(dst[1], dst[0], shape[2])
+    assert np.array_equal(got, want), int(np.abs(got.astype(int) - want.astype(int)).max())
+
+
+def test_dmb_reader_rejects_bad_headers(tmp_path):
+    def write(name, hdr, payload):
+        p = str(tmp_path / name)
+        with open(p, "wb") as f:
+            f.write(np.asarray(hdr, np.int32).tobytes() + payload)
+        return p
+    ok1 = write("d.dmb", [1, 3, 4, 1], np.zeros(12, np.float32).tobytes())
+    ok3 = write("n.dmb", [1, 3, 4, 3], np.zeros(36, np.float32).tobytes())
+    run = lambda p, kind: subprocess.run([EXE, "--dmb", p, kind], capture_output=True, text=True).returncode  # noqa: E731
+    assert run(ok1, "depth") == 0 and run(ok3, "normal") == 0 and run(ok1, "any") == 0
+    assert run(ok3, "depth") != 0 and run(ok1, "normal") != 0            # channel count is part of the contract
+    assert run(write("neg.dmb", [1, -3, 4, 1], b""), "any") != 0
+    assert run(write("huge.dmb", [1, 2 ** 30, 2 ** 30, 1], b""), "any") != 0
+    assert run(write("ch.dmb", [1, 3, 4, 2], np.zeros(24, np.float32).tobytes()), "any") != 0
+    assert run(write("type.dmb", [2, 3, 4, 1], np.zeros(12, np.float32).tobytes()), "any") != 0
+    assert run(write("short.dmb", [1, 3, 4, 1], np.zeros(5, np.float32).tobytes()), "any") != 0

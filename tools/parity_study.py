@@ -39,6 +39,9 @@ import refbind  # noqa: E402
 from gpu_parity import bits, color_mask, interior, gt_planes, problem, depth_normal_tol, plane_stats  # noqa: E402
 
 
+WAVE_BLOCKS = 148   # resident blocks of the reference launch on a B200 (1 x 512 threads x 128 registers per SM)
+
+
 def ref_set_state(ref, st):
     ref.set_planes(0, st[0])
     ref.set_scalars(0, st[1])
@@ -68,6 +71,12 @@ def half_sweeps(ref, mine, h, w, masks=None, dump=None, dump_key=""):
             mine.set_state(*S)
             mine.run_sweep_snapshot(it, color, R[0], R[1])
             Mn = mine.get_state()
+            mine.SetWaveEmulation(WAVE_BLOCKS)          # the reference launch's block waves, one sub-launch each
+            mine.set_state(*S)
+            mine.run_sweep(it, color)
+            Mw = mine.get_state()
+            mine.SetWaveEmulation(0)
+            eq_wave = (bits(Mw[0]) == bits(R[0])).all(-1)
             cm = color_mask(h, w, color)
             inner = cm & interior(h, w, 4)
             eq_old = (bits(Mo[0]) == bits(R[0])).all(-1)
@@ -82,6 +91,9 @@ def half_sweeps(ref, mine, h, w, masks=None, dump=None, dump_key=""):
                 "explained_by_new_reads": float((~eq_old & eq_new)[inner].mean()),
                 "unexplained": float(unexpl[inner].mean()),
                 "ref_rerun_equal": float(eq_self[inner].mean()),
+                "equal_wave_emulation": float(eq_wave[inner].mean()),
+                "wave_differs_y_mod32": np.bincount(np.nonzero(inner & ~eq_wave)[0] % 32, minlength=32).tolist(),
+                "wave_differs_by_wave": np.bincount((((np.nonzero(inner & ~eq_wave)[0] >> 5) * ((w + 31) // 32) + (np.nonzero(inner & ~eq_wave)[1] >> 5)) // WAVE_BLOCKS), minlength=1).tolist(),
                 # pixels where the reference agrees with itself yet not with either product variant
                 "unexplained_where_ref_is_stable": float((unexpl & eq_self)[inner].mean()),
                 "rng_equal_old": float((Mo[3] == R[3]).all(-1)[inner].mean()),
@@ -98,7 +110,8 @@ def half_sweeps(ref, mine, h, w, masks=None, dump=None, dump_key=""):
                 for name, mk in (("covered", masks > 0), ("uncovered", masks == 0)):
                     sel = inner & mk
                     r[name] = {"pixels": int(sel.sum()), "equal_old": float(eq_old[sel].mean()), "explained_by_new_reads": float((~eq_old & eq_new)[sel].mean()),
-                               "unexplained": float(unexpl[sel].mean()), "ref_rerun_equal": float(eq_self[sel].mean())}
+                               "unexplained": float(unexpl[sel].mean()), "ref_rerun_equal": float(eq_self[sel].mean()),
+                               "equal_wave_emulation": float(eq_wave[sel].mean())}
             res[f"it{it}_c{color}"] = r
             if dump is not None and it == 0:
                 k = f"{dump_key}_c{color}_"
@@ -203,11 +216,17 @@ def study(scene, view, seed, dump=None):
         m.RunPatchMatch(seed)
         tm = m.last_timing()
         mp = m.get_state()[0]
+        m.SetWaveEmulation(WAVE_BLOCKS)
+        m.RunPatchMatch(seed)
+        m.RunPatchMatch(seed)
+        tmw = m.last_timing()
+        mw = m.get_state()[0]
         m.close()
-        r = {"ref_ms": [ms_a, ms_b], "ours_ms": tm}
+        r = {"ref_ms": [ms_a, ms_b], "ours_ms": tm, "ours_wave_emulation_ms": tmw}
         for b in (8, 32):
             inner = interior(h, w, b)
             r[f"interior{b}"] = {"ours_vs_ref": {"plane_bit_equal": plane_stats(mp, ra, inner), **depth_normal_tol(mp, ra, inner)},
+                                 "ours_wave_emulation_vs_ref": {"plane_bit_equal": plane_stats(mw, ra, inner), **depth_normal_tol(mw, ra, inner)},
                                  "ref_vs_ref": {"plane_bit_equal": plane_stats(ra, rb, inner), **depth_normal_tol(ra, rb, inner)}}
         gt = depths[0]
         inner = interior(h, w, 8)
@@ -251,7 +270,7 @@ def main():
         print(cfg, json.dumps(short), flush=True)
         for mode in ("photometric", "geom", "prior"):
             for k, r in report[cfg].get(mode, {}).items():
-                print(f"  {mode} {k}: old {r['equal_old']:.4f} +new {r['explained_by_new_reads']:.4f} unexplained {r['unexplained']:.4f} "
+                print(f"  {mode} {k}: old {r['equal_old']:.4f} +new {r['explained_by_new_reads']:.4f} unexplained {r['unexplained']:.4f} | wave-emulation {r['equal_wave_emulation']:.4f} | "
                       f"(ref stable there {r['unexplained_where_ref_is_stable']:.4f}) ref-rerun {r['ref_rerun_equal']:.4f}", flush=True)
 
 
