@@ -52,7 +52,7 @@ oracle/liboracle.so: $(wildcard oracle/*.c) $(wildcard oracle/*.h)
 
 # The reference's own kernels, compiled from where they lie (never copied into the
 # repo), sm_100 + the reference's flags; only built where /root/reference exists.
-ref: oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so
+ref: oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so oracle/_ref/libacmmp_ref_full_p2.so
 oracle/_ref/libacmmp_ref.so: oracle/ref_harness.cu $(wildcard oracle/ref_stub/opencv2/*.hpp)
 	@if [ -d $(REF) ]; then mkdir -p oracle/_ref && \
 	$(NVCC) -O3 --use_fast_math --maxrregcount=128 -std=c++14 -gencode arch=compute_100,code=sm_100 \
@@ -65,6 +65,18 @@ oracle/_ref/libacmmp_ref_full.so: oracle/ref_full_harness.cu acmmp_b200/csrc/pri
 	@if [ -d $(REF) ]; then mkdir -p oracle/_ref && \
 	$(NVCC) -O3 --use_fast_math --maxrregcount=128 -std=c++14 -gencode arch=compute_100,code=sm_100 -w \
 	  -Ioracle/ref_stub -I$(REF) -Iinclude -Xcompiler -fPIC -shared -o $@ oracle/ref_full_harness.cu acmmp_b200/csrc/prior.cpp -lcudart ; \
+	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
+
+# The same program with patch P2 of BASELINE.md: `#define DEBUG` (ACMMP.cu:3) removed.  The patched translation unit is
+# GENERATED at build time into the git-ignored oracle/_ref/gen_p2/ (sed deletes that one line; removed again after the
+# compile); it is found first on the
+# include path, everything else still comes from $(REF).
+oracle/_ref/libacmmp_ref_full_p2.so: oracle/ref_full_harness.cu acmmp_b200/csrc/prior.cpp $(wildcard oracle/ref_stub/opencv2/*.hpp)
+	@if [ -d $(REF) ]; then mkdir -p oracle/_ref/gen_p2 && \
+	sed '/^#define DEBUG/d' $(REF)/ACMMP.cu > oracle/_ref/gen_p2/ACMMP.cu && ! grep -q '^#define DEBUG' oracle/_ref/gen_p2/ACMMP.cu && \
+	$(NVCC) -O3 --use_fast_math --maxrregcount=128 -std=c++14 -gencode arch=compute_100,code=sm_100 -w \
+	  -Ioracle/_ref/gen_p2 -Ioracle/ref_stub -I$(REF) -Iinclude -Xcompiler -fPIC -shared -o $@ oracle/ref_full_harness.cu acmmp_b200/csrc/prior.cpp -lcudart ; \
+	rc=$$?; rm -rf oracle/_ref/gen_p2; exit $$rc; \
 	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
 
 # The reference's HOST code (RunFusion + helpers: ACMMP.cpp, acmmp_definitions.cpp) against the
@@ -82,5 +94,5 @@ oracle/_ref/libacmmp_ref_host_ieee.so: $(REF_HOST_SRC)
 	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
 
 clean:
-	rm -f $(LIB) build/fusion.o build/pairs.o build/seeded.o oracle/liboracle.so oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so
+	rm -f $(LIB) build/fusion.o build/pairs.o build/seeded.o oracle/liboracle.so oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so oracle/_ref/libacmmp_ref_full_p2.so
 .PHONY: all oracle ref cli clean

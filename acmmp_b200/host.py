@@ -383,6 +383,14 @@ class Scan:
     def num_levels(self):
         return self._lib.acmmp_scan_num_levels(self._s)
 
+    def set_sequential_geom(self, on):
+        """geom-1 order: True = the reference's in-place order, False = Jacobi, None = the default (in place when unsharded)"""
+        self._ck(self._lib.acmmp_scan_set_sequential_geom(self._s, -1 if on is None else int(bool(on))), "set_sequential_geom")
+
+    def set_schedule(self, single_scale=False, photometric_only=False):
+        """reduced schedules (before the first level): no pyramid / photometric stage without the planar prior"""
+        self._ck(self._lib.acmmp_scan_set_schedule(self._s, int(bool(single_scale)), int(bool(photometric_only))), "set_schedule")
+
     def begin_level(self, level):
         self._ck(self._lib.acmmp_scan_begin_level(self._s, level), "begin_level")
 

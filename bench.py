@@ -33,22 +33,52 @@ SWEEP_DRAM_BYTES_PER_LAUNCH_U8 = 215e6   # profiles/r1o_sweep_u8_full_summary.tx
 HYP_PER_RUN = 29               # 1 (init) + 2 x 14; 30 for the hierarchy (upsample-init) run
 
 
+# BASELINE.json `configs`: the workload each --config runs (views, width, height, sources, camera layout)
+CONFIGS = {
+    # configs[2], the one `metric` is quoted on (default)
+    "full": dict(views=49, width=1600, height=1200, nsrc=10, layout="grid",
+                 name="configs[2]: DTU-shape {W}x{H} x {n} views, {ns} sources, full ACMMP ({nl} scales x (photometric+planar prior, geom x2))",
+                 metric="views/s, DTU-shape 1600x1200 49-view full ACMMP (multi-scale + planar prior + geometric consistency)"),
+    # configs[1]: isolates RunPatchMatch (ACMMP.cu:1378-1456) from the schedule - the kernel-vs-kernel line
+    "photometric": dict(views=49, width=1600, height=1200, nsrc=10, layout="grid",
+                        name="configs[1]: DTU-shape {W}x{H} x {n} views, {ns} sources, single scale, photometric only (one RunPatchMatch per view)",
+                        metric="views/s, DTU-shape 1600x1200 49-view single-scale photometric PatchMatch"),
+    # configs[3]: 6048x4032 is capped to 3200 (ACMMP.h:36) -> 3 scales, 2 JBU steps
+    "eth3d": dict(views=11, width=6048, height=4032, nsrc=10, layout="grid",
+                  name="configs[3]: ETH3D-high-res-shape {W}x{H} x {n} views, {ns} sources, full ACMMP ({nl} scales, JBU between them)",
+                  metric="views/s, ETH3D-shape 6048x4032 11-view full ACMMP (3 scales + JBU)"),
+    # configs[4]
+    "tnt": dict(views=300, width=1920, height=1080, nsrc=20, layout="ring",
+                name="configs[4]: Tanks&Temples-shape {W}x{H} x {n} views, {ns} sources, full ACMMP ({nl} scales) + fusion",
+                metric="views/s, Tanks&Temples-shape 1920x1080 300-view full ACMMP + fusion"),
+}
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--views", type=int, default=49)
-    ap.add_argument("--width", type=int, default=1600)
-    ap.add_argument("--height", type=int, default=1200)
-    ap.add_argument("--nsrc", type=int, default=10)
+    ap.add_argument("--config", default="full", choices=sorted(CONFIGS))
+    ap.add_argument("--views", type=int, default=None)
+    ap.add_argument("--width", type=int, default=None)
+    ap.add_argument("--height", type=int, default=None)
+    ap.add_argument("--nsrc", type=int, default=None)
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tex-format", default="auto", choices=["auto", "r32f"],
                     help="auto: R8 unorm texels on levels that are not resized (bit-identical samples); r32f: float texels everywhere")
-    ap.add_argument("--ref-views", type=int, default=4, help="views per step of the reference arm (bounded sample)")
-    return ap.parse_args()
+    ap.add_argument("--ref-views", type=int, default=4, help="views of the reference arm's kernel-only pass (bounded sample)")
+    ap.add_argument("--ref-full-scan", action="store_true", help="reference arm: every view of the scan per step instead of the bounded sub-scan")
+    ap.add_argument("--no-ref-p2", action="store_true", help="reference arm: skip the extra step with patch P2 (#define DEBUG removed)")
+    args = ap.parse_args()
+    preset = CONFIGS[args.config]
+    for k in ("views", "width", "height", "nsrc"):
+        if getattr(args, k) is None:
+            setattr(args, k, preset[k])
+    args.layout = preset["layout"]
+    return args
 
 
 class ClockSampler:
@@ -108,7 +138,7 @@ def make_scan_inputs(args, device):
     depth range as in DTU cam files, 10 nearest views as sources; rendered on the
     device, integer-valued grey images like decoded JPEGs."""
     from acmmp_b200.scene import make_scene
-    sc = make_scene(args.views, args.width, args.height, args.nsrc, seed=args.seed, device=device, as_numpy=False)
+    sc = make_scene(args.views, args.width, args.height, args.nsrc, seed=args.seed, device=device, as_numpy=False, layout=args.layout)
     return sc
 
 
@@ -119,12 +149,12 @@ class DevPtr:
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
 
 
-def hyp_evals_per_view(scan_sizes):
-    """(w, h) per level -> hypothesis evaluations of one view of full ACMMP: 4 runs
-    per level, 29 per pixel per run, 30 for the hierarchy run."""
+def hyp_evals_per_view(scan_sizes, runs_per_level=4):
+    """(w, h) per level -> hypothesis evaluations of one view: `runs_per_level` RunPatchMatch per level (4 in full
+    ACMMP, 1 in the photometric-only schedule), 29 per pixel per run, 30 for the hierarchy run."""
     total = 0
     for lvl, (w, h) in enumerate(scan_sizes):
-        total += w * h * (4 * HYP_PER_RUN + (1 if lvl > 0 else 0))
+        total += w * h * (runs_per_level * HYP_PER_RUN + (1 if lvl > 0 else 0))
     return total
 
 
@@ -147,14 +177,31 @@ def run_ours(args):
     from acmmp_b200 import lib as L
     scan = host.Scan(sc["cams"], sc["pairs"], device=local, rank=rank, world=world,
                      tex_format=L.TEX_R32F if args.tex_format == "r32f" else L.TEX_AUTO)
+    photo_only = args.config == "photometric"
+    if photo_only:
+        scan.set_schedule(single_scale=True, photometric_only=True)
+    stages = (host.STAGE_PHOTO,) if photo_only else (host.STAGE_PHOTO, host.STAGE_GEOM0, host.STAGE_GEOM1)
+    runs_per_level = 1 if photo_only else 4            # RunPatchMatch per view per level
     owned = scan.owned()
-    H, W = args.height, args.width
+    # size of the maps a step hands back = the finest level (the 3200 cap of ACMMP.h:36 applies to eth3d)
+    cap = 3200
+    fmax = max(args.width, args.height)
+    if fmax > cap:
+        f = min(np.float32(cap) / np.float32(args.width), np.float32(cap) / np.float32(args.height))
+        W, H = int(round(float(np.float32(args.width) * f))), int(round(float(np.float32(args.height) * f)))
+    else:
+        W, H = args.width, args.height
     outs = {v: (torch.empty((H, W), dtype=torch.float32).pin_memory().numpy(),
                 torch.empty((H, W, 3), dtype=torch.float32).pin_memory().numpy(),
                 torch.empty((H, W), dtype=torch.float32).pin_memory().numpy()) for v in owned}
     n_exchanges = [0]
 
     def exchange(ptr, stride, slots):
+        if photo_only:          # no stage reads another view's depth map in the photometric-only schedule
+            return
+        gather(ptr, stride, slots)
+
+    def gather(ptr, stride, slots):
         if world == 1:
             return
         seg = int(stride) * int(slots)
@@ -183,7 +230,7 @@ def run_ours(args):
                 scan.set_image_u8(v, imgs_np[v], sync=False)
             else:
                 scan.set_image(v, imgs_dev[v].data_ptr(), on_device=True)
-        scan.run_all(seed=1234, exchange=exchange, level_done=level_done)
+        scan.run_all(seed=1234, exchange=exchange, level_done=level_done, stages=stages)
         if e2e:
             for v in owned:
                 scan.get_view(v, out=outs[v])
@@ -237,7 +284,7 @@ def run_ours(args):
     scan.reset()
     for v in range(n):
         scan.set_image(v, imgs_dev[v].data_ptr(), on_device=True)
-    scan.run_all(seed=1234, exchange=exchange, level_done=count_level)
+    scan.run_all(seed=1234, exchange=exchange, level_done=count_level, stages=stages)
     scan.sync()
     exchanges_per_step = n_exchanges[0] - ex0
     ncc = {k: sum(c[k] for c in ncc_level.values()) for k in ("init", "sweeps")}
@@ -250,7 +297,7 @@ def run_ours(args):
     top_u8 = bool(level_u8.get(top, False))
     top_sweep_s = level_tm_timed[top]["sweeps_ms"] * 1e-3
     top_fetches = ncc_level[top]["sweeps"] * 36 * args.steps
-    top_launches = 4 * 4 * len(owned) * args.steps
+    top_launches = runs_per_level * 4 * len(owned) * args.steps   # 4 half-sweeps per RunPatchMatch
     top_peak, top_grouped = (tex8_coherent, tex8_grouped) if top_u8 else (tex_coherent, tex_grouped)
     top_achieved = top_fetches / top_sweep_s / 1e9
     per_level = []
@@ -259,40 +306,46 @@ def run_ours(args):
         per_level.append({"level": lv, "size": list(sizes[lv]), "texels": "R8 unorm" if level_u8.get(lv) else "R32F",
                           "sweeps_ms_per_step": s_ms / args.steps, "init_ms_per_step": level_tm_timed[lv]["init_ms"] / args.steps,
                           "gfetch_per_s": ncc_level[lv]["sweeps"] * 36 * args.steps / (s_ms * 1e-3) / 1e9})
-    hpv = hyp_evals_per_view(sizes)
+    hpv = hyp_evals_per_view(sizes, runs_per_level)
     views_per_s = n * args.steps / (ms_dev * 1e-3)
     e2e_views_per_s = n * args.steps / (ms_e2e * 1e-3)
     # dominant kernel: sweep_kernel (rank 0's launches in the timed region).
     #  reference formulation: per run P * 28 hypotheses * nsrc views, 1538 flop each
     #  executed: counted NCC evaluations x 36 bilinear fetches (the kernel scores the current plane and
     #  the 5 refinement candidates against the sampled views only)
-    ncc_sweeps = sum(4 * w * h * 28 * args.nsrc for (w, h) in sizes) * len(owned) * args.steps
+    ncc_sweeps = sum(runs_per_level * w * h * 28 * args.nsrc for (w, h) in sizes) * len(owned) * args.steps
     sweep_s = tm["sweeps_ms"] * 1e-3
     fp32_achieved = ncc_sweeps * FLOP_PER_NCC / sweep_s / 1e12
     fetches = ncc["sweeps"] * 36 * args.steps
     tex_achieved = fetches / sweep_s / 1e9
-    n_sweep_launches = 4 * 4 * len(owned) * len(sizes) * args.steps   # 4 runs x 4 half-sweeps per view per level
+    n_sweep_launches = runs_per_level * 4 * len(owned) * len(sizes) * args.steps   # runs x 4 half-sweeps per view per level
     h2d = sum(int(np.prod(im.shape)) for im in imgs_np)   # uint8
     d2h = len(owned) * H * W * 5 * 4
     line = {
-        "metric": "views/s, DTU-shape 1600x1200 49-view full ACMMP (multi-scale + planar prior + geometric consistency)",
+        "metric": CONFIGS[args.config]["metric"],
         "value": views_per_s, "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"configs[2]: DTU-shape {W}x{H} x {n} views, {args.nsrc} sources, full ACMMP "
-                               f"({len(sizes)} scales x (photometric+planar prior, geom x2))",
-                   "levels": [list(s) for s in sizes], "sharding": f"view % {world}", "exchange": "nccl all_gather of depth maps per stage",
+        "config": {"workload": CONFIGS[args.config]["name"].format(W=args.width, H=args.height, n=n, ns=args.nsrc, nl=len(sizes)),
+                   "name": args.config,
+                   "geom1_order": "in place (the reference's Gauss-Seidel order)" if world == 1 else "Jacobi (sharded scan)",
+                   "levels": [list(s) for s in sizes], "sharding": f"view % {world}", "exchange": "none (no stage reads another view's maps)" if photo_only else "nccl all_gather of depth maps per stage",
                    "texels": [p["texels"] for p in per_level],
-                   "l2": "inputs (49 x 7.7 MB images + per-view state) exceed the 126 MB L2; no explicit flush",
+                   "l2": "inputs (%d images of %.1f MB + per-view state) exceed the 126 MB L2; no explicit flush" % (n, args.width * args.height * 4 / 1e6),
                    "hyp_evals_per_view": hpv},
         "mpix_hyp_per_s": views_per_s * hpv / 1e6,
         "e2e": {"value": e2e_views_per_s, "unit": "views/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / args.steps, "mpix_hyp_per_s": e2e_views_per_s * hpv / 1e6},
         "gpu_launches": int(launches),
         "kernel_ms_per_step": {k: tm[k] / args.steps for k in ("init_ms", "sweeps_ms", "tail_ms", "total_ms")},
+        # the RunPatchMatch kernels alone (CUDA events around init / sweeps / tail of every run, this rank): what the
+        # reference arm's `kernel_only` is compared with - the rest of `value` is schedule (prior construction, JBU, copies)
+        "kernel_only": {"value": len(owned) * args.steps / (tm["total_ms"] * 1e-3), "unit": "views/s (this rank's views / its RunPatchMatch kernel time)",
+                        "ms_per_view": tm["total_ms"] / (len(owned) * args.steps)},
         "roofline": {"bound": "tex", "kernel": "sweep_kernel<%s> at %dx%d" % ("R8" if top_u8 else "R32F", sizes[top][0], sizes[top][1]),
                      "achieved": top_achieved, "peak": top_peak, "unit": "Gfetch/s",
-                     "frac": top_achieved / top_peak, "traffic": SWEEP_DRAM_BYTES_PER_LAUNCH_U8 if top_u8 else SWEEP_DRAM_BYTES_PER_LAUNCH,
+                     "frac": top_achieved / top_peak,
+                     "traffic": (SWEEP_DRAM_BYTES_PER_LAUNCH_U8 if top_u8 else SWEEP_DRAM_BYTES_PER_LAUNCH) if (tuple(sizes[top]) == (1600, 1200) and args.nsrc == 10) else None,
                      "launches": top_launches, "avg_launch_ms": level_tm_timed[top]["sweeps_ms"] / top_launches,
                      "fetches_per_launch": top_fetches / top_launches, "peak_grouped_access": top_grouped,
                      "share_of_kernel_time": level_tm_timed[top]["sweeps_ms"] / tm["total_ms"],
@@ -316,8 +369,13 @@ def run_ours(args):
     # bit-level checksum of the final maps of every view (depth from this rank's exchange buffer, i.e.
     # through the NCCL gathers; normals and costs of the owned views summed over ranks): equal numbers
     # at different --gpus mean the sharded run reproduces the single-GPU maps bit for bit
+    # (geom-1 in Jacobi order at every N for this pass: the unsharded default is the reference's in-place order,
+    # which a sharded scan cannot follow)
+    scan.set_sequential_geom(False)
     scan.reset()
-    scan.run_all(seed=1234, exchange=exchange)
+    scan.run_all(seed=1234, exchange=exchange, stages=stages)
+    if photo_only:
+        gather(*scan.exchange_info())
     scan.sync()
     csum = torch.zeros(1, dtype=torch.int64, device=dev)
     for v in range(n):
@@ -365,7 +423,7 @@ def run_ours(args):
         line["fusion"] = {"points": int(npts), "ms": fwall * 1e3, "device_ms": fst["score_ms"] + fst["greedy_ms"] + fst["emit_ms"],
                           "fixed_point_rounds_max": max(fst["rounds"]), "consistency_scalar": 0.3, "num_consistent_thresh": 1,
                           "where": "rank 0" + (" after gathering the normals over NCCL" if world > 1 else "")}
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and args.config == "full":
             import oraclebind as ob
             maps = [scan.get_view(v, want_cost=False) for v in range(n)]
             t0 = time.time()
@@ -373,7 +431,8 @@ def run_ours(args):
             line["fusion"].update({"cpu_port_s": time.time() - t0, "cpu_port_points": int(cnt), "cpu_cores": 1})
         fus.close()
     if rank == 0 and not args.no_cpu_baseline:
-        line["planar_prior"] = planar_prior_baseline(args, sc)
+        if args.config in ("full", "photometric"):
+            line["planar_prior"] = planar_prior_baseline(args, sc)
         line["cpu_baseline"] = cpu_baseline(args, sc, hpv)
     if rank == 0:
         print(json.dumps(line), flush=True)
@@ -458,18 +517,43 @@ def cpu_baseline(args, sc, hyp_per_view):
             "note": "the reference has no CPU PatchMatch; this is the oracle restatement (exact libm, no SIMD)"}
 
 
+def level_sizes(W, H, single_scale=False, cap=3200, bound=1000):
+    """(w, h) of every pyramid level of a W x H view, coarse to fine (ComputeMultiScaleSettings + InputInitialization)"""
+    m = min(max(W, H), cap)
+    k = 0
+    while m > bound and not single_scale:
+        m //= 2
+        k += 1
+    out = []
+    for lvl in range(k, -1, -1):
+        size = int(min(max(W, H), cap) / 2 ** lvl)
+        if W <= size and H <= size:
+            out.append((W, H))
+        else:
+            f = min(np.float32(size) / np.float32(W), np.float32(size) / np.float32(H))
+            out.append((int(round(float(np.float32(W) * f))), int(round(float(np.float32(H) * f)))))
+    return out
+
+
 def run_reference(args):
-    """Baseline arm.  Preferred: the reference PROGRAM itself (oracle/_ref/libacmmp_ref_full.so: its
-    kernels, host class, ProcessProblem, JointBilateralUpsampling and RunFusion compiled from where
-    they lie, run in the order of its main() on its own on-disk layout, .dmb round trips included).
-    Each step = the whole schedule over a bounded sub-scan: the centre view of the rig and its
-    sources (nsrc + 1 views, every view paired with all the others), i.e. the per-view work of the
-    full scan.  1 GPU: the reference has no multi-GPU mode and no CPU PatchMatch."""
+    """Baseline arm, 1 GPU (the reference has no multi-GPU mode and no CPU PatchMatch): the reference's own code on
+    this box, compiled from where it lies by `make ref`.
+    --config photometric: its kernels in the order of ACMMP::RunPatchMatch, per view its own problem set-up
+    (textures, buffers) and result copy (oracle/_ref/libacmmp_ref.so), every view of the scan per step.
+    other configs: the reference PROGRAM (oracle/_ref/libacmmp_ref_full.so: kernels, host class, ProcessProblem,
+    JointBilateralUpsampling, RunFusion, run in the order of its main() on its own on-disk layout, .dmb round trips
+    included).  Each step = the whole schedule over a bounded sub-scan: the centre view of the rig and its sources
+    (nsrc + 1 views, every view paired with all the others) = the per-view work of the full scan; --ref-full-scan
+    runs all views.  Beside `value`: `p2` = one more step of the same program built without `#define DEBUG`
+    (BASELINE.md patch P2), `kernel_only` = its RunPatchMatch kernels alone (CUDA events; the kernels harness in the
+    reference's per-view flow on --ref-views views), `delaunay_standin_share`."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import refbind
+    if args.config == "photometric":
+        return run_reference_photometric(args)
     if not refbind.full_available():
         return run_reference_kernels(args)
     import shutil
@@ -479,46 +563,152 @@ def run_reference(args):
     sc = make_scan_inputs(args, torch.device("cuda", 0))
     n = args.views
     centre = n // 2
-    sample = sorted(set([centre] + sc["pairs"][centre][:args.nsrc]))
+    sample = list(range(n)) if args.ref_full_scan else sorted(set([centre] + sc["pairs"][centre][:args.nsrc]))
     images = [sc["images"][i].cpu().numpy() for i in sample]
     cams = [sc["cams"][i] for i in sample]
-    pairs = [[j for j in range(len(sample)) if j != i] for i in range(len(sample))]
+    if args.ref_full_scan:
+        pairs = sc["pairs"]
+    else:
+        pairs = [[j for j in range(len(sample)) if j != i] for i in range(len(sample))]
     H, W = args.height, args.width
-    sizes = [(W // 2, H // 2), (W, H)] if max(W, H) > 1000 else [(W, H)]
+    sizes = level_sizes(W, H)
     hpv = hyp_evals_per_view(sizes)
+    # same number of warm-up passes as the product's arm for the config the driver runs; the long configs keep one
+    warm = args.warmup if (args.config == "full" and not args.ref_full_scan) else min(args.warmup, 1)
     dense = tempfile.mkdtemp(prefix="acmmp_ref_")
+    p2 = None
     try:
         refbind.write_dense_folder(dense, cams, images, pairs)
-        for _ in range(min(args.warmup, 1)):     # a synchronous, allocation-per-view flow: one warm-up pass is enough
+        for _ in range(warm):
             refbind.full_run(dense, seed=1234, fuse=False)
         t_pm = 0.0
         t_fu = 0.0
+        refbind.full_delaunay_seconds()
         with ClockSampler(0) as clocks:
             for k in range(args.steps):
                 a, b = refbind.full_run(dense, seed=1234 + k, fuse=(k == args.steps - 1))
                 t_pm += a
                 t_fu = b
+        t_del = refbind.full_delaunay_seconds()
         npts = len(refbind.read_ply(os.path.join(dense, "ACMMP", "ACMMP_model.ply"))[0])
+        if refbind.full_available("p2") and not args.no_ref_p2:
+            refbind.full_run(dense, seed=1234, fuse=False, variant="p2")
+            a, _ = refbind.full_run(dense, seed=1234, fuse=False, variant="p2")
+            p2 = {"value": len(sample) / a, "unit": "views/s", "ms_per_step": a * 1e3, "steps": 1, "warmup": 1,
+                  "what": "the same program built without `#define DEBUG` (ACMMP.cu:3; BASELINE.md patch P2): no per-run debug copies of the plane map"}
     finally:
         shutil.rmtree(dense, ignore_errors=True)
     v = len(sample) * args.steps / t_pm
+    kernel_only = None
+    if args.config == "full" and refbind.available():
+        kernel_only = reference_kernel_only(args, sc)
     line = {
         "impl": "reference",
-        "metric": "views/s, DTU-shape 1600x1200 49-view full ACMMP (multi-scale + planar prior + geometric consistency)",
-        "value": v, "unit": "views/s", "n_gpus": 1, "steps": args.steps, "warmup": min(args.warmup, 1),
+        "metric": CONFIGS[args.config]["metric"],
+        "value": v, "unit": "views/s", "n_gpus": 1, "steps": args.steps, "warmup": warm,
         "ms_per_step": t_pm / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"configs[2]: DTU-shape {W}x{H} x {n} views, {args.nsrc} sources, full ACMMP", "levels": [list(x) for x in sizes],
-                   "sample_views": sample, "hyp_evals_per_view": hpv,
-                   "what": "the reference program (ACMMP.cu / ACMMP.cpp / acmmp_definitions.cpp compiled from where they lie, sm_100, its own flags) "
-                           "in the order of its main(): per view and stage its own image read + resize, texture set-up, RunPatchMatch, host "
-                           "planar prior and .dmb round trips; stand-ins: raw images instead of JPEG decode, the product's Delaunay for "
-                           "cv::Subdiv2D, inert imshow / imwrite, fixed seed"},
+        "config": {"workload": CONFIGS[args.config]["name"].format(W=W, H=H, n=n, ns=args.nsrc, nl=len(sizes)), "name": args.config,
+                   "levels": [list(x) for x in sizes], "sample_views": sample, "hyp_evals_per_view": hpv,
+                   "what": "the reference program (ACMMP.cu / ACMMP.cpp / acmmp_definitions.cpp compiled from where they lie, sm_100, its own flags, "
+                           "`#define DEBUG` as shipped) in the order of its main(): per view and stage its own image read + resize, texture set-up, "
+                           "RunPatchMatch, host planar prior and .dmb round trips; stand-ins: raw images instead of JPEG decode, the product's "
+                           "Delaunay for cv::Subdiv2D (share of the step: delaunay_standin_share), inert imshow / imwrite, fixed seed"},
         "mpix_hyp_per_s": v * hpv / 1e6,
-        "fusion": {"points": npts, "ms": t_fu * 1e3, "what": "its own RunFusion (CPU, 1 thread) on the sub-scan"},
+        "delaunay_standin_share": t_del / t_pm,
+        "fusion": {"points": npts, "ms": t_fu * 1e3, "what": "its own RunFusion (CPU, 1 thread) on the sample"},
         "cpu_baseline": {"value": v, "unit": "views/s", "cores": 1, "kind": "reference",
-                         "sample": f"{len(sample)}-view sub-scan per step (view {centre} and its {args.nsrc} sources, every view paired with all the "
-                                   "others), all scales and stages; 1 B200 for the reference's CUDA kernels, 1 host thread for its CPU steps"},
+                         "sample": (f"all {n} views per step" if args.ref_full_scan else
+                                    f"{len(sample)}-view sub-scan per step (view {centre} and its {args.nsrc} sources, every view paired with all the others)")
+                                   + ", all scales and stages; 1 B200 for the reference's CUDA kernels, 1 host thread for its CPU steps"},
+        "e2e": {"value": v, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "clocks": clocks.summary(),
+    }
+    if p2 is not None:
+        line["p2"] = p2
+    if kernel_only is not None:
+        line["kernel_only"] = kernel_only
+    print(json.dumps(line), flush=True)
+
+
+def reference_kernel_only(args, sc):
+    """RunPatchMatch kernels of the reference alone: oracle/_ref/libacmmp_ref.so (its __global__ functions launched in the
+    order of ACMMP::RunPatchMatch, CUDA events around each run) in the reference's per-view / per-stage flow
+    (oracle/ref_pipeline.py) on --ref-views views; views outside the sample contribute ground-truth depth maps to the
+    geometric-consistency stages, so a view's kernel work is that of the full scan."""
+    import cv2
+    import ref_pipeline
+    import torch
+    images = [im.cpu().numpy() for im in sc["images"]]
+    gts = [d.cpu().numpy() for d in sc["depths"]]
+    n = args.views
+    centre = n // 2
+    sample = sorted(set([centre] + sc["pairs"][centre][:max(0, args.ref_views - 1)]))
+    rs = ref_pipeline.RefScan(images, sc["cams"], sc["pairs"], 0)
+
+    def external(i, w, h):
+        g = gts[i]
+        return g if g.shape == (h, w) else cv2.resize(g, (w, h), interpolation=cv2.INTER_NEAREST)
+
+    rs.run_all(1234, sample[:1], external)       # warm-up
+    torch.cuda.synchronize()
+    rs.kernel_ms, rs.prior_s, rs.runs = 0.0, 0.0, 0
+    rs.run_all(1234, sample, external)
+    torch.cuda.synchronize()
+    return {"value": len(sample) / (rs.kernel_ms * 1e-3), "unit": "views/s (views / RunPatchMatch kernel time)",
+            "ms_per_view": rs.kernel_ms / len(sample), "runs": rs.runs, "views": sample,
+            "how": "reference kernels (libacmmp_ref.so) in the reference's per-view flow, CUDA events around each RunPatchMatch"}
+
+
+def run_reference_photometric(args):
+    """configs[1]: one RunPatchMatch per view, single scale, no prior, no geometric consistency - the reference's kernels in the
+    order of ACMMP::RunPatchMatch, with its per-view problem set-up (one texture per image, buffers: ACMMP.cpp:638-708) and the
+    result copy (ACMMP.cu:1453-1455).  Every view of the scan per step (same config as the product's arm)."""
+    import refbind
+    import torch
+    torch.cuda.set_device(0)
+    sc = make_scan_inputs(args, torch.device("cuda", 0))
+    n = args.views
+    images = [im.cpu().numpy() for im in sc["images"]]
+    ref = refbind.RefACMMP(0)
+    W, H = args.width, args.height
+    hpv = hyp_evals_per_view([(W, H)], 1)
+
+    def step(seed):
+        kms = 0.0
+        for v in range(n):
+            ids = [v] + sc["pairs"][v]
+            ref.set_problem([images[i] for i in ids], [sc["cams"][i] for i in ids])
+            kms += ref.run(seed + v)
+            ref.get_result()
+        return kms
+
+    for _ in range(args.warmup):
+        step(1234)
+    torch.cuda.synchronize()
+    kernel_ms = 0.0
+    with ClockSampler(0) as clocks:
+        t0 = time.time()
+        for k in range(args.steps):
+            kernel_ms += step(1234 + k)
+        torch.cuda.synchronize()
+        dt = time.time() - t0
+    ref.close()
+    v = n * args.steps / dt
+    line = {
+        "impl": "reference", "metric": CONFIGS[args.config]["metric"],
+        "value": v, "unit": "views/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": CONFIGS[args.config]["name"].format(W=W, H=H, n=n, ns=args.nsrc, nl=1), "name": args.config, "levels": [[W, H]],
+                   "hyp_evals_per_view": hpv,
+                   "what": "reference ACMMP.cu kernels (sm_100, -O3 --use_fast_math --maxrregcount=128) launched in the order of ACMMP::RunPatchMatch "
+                           "with a device-wide synchronisation after each (ACMMP.cu:1415-1448), per view its texture / buffer set-up from host "
+                           "images and the D2H of planes + costs; wall clock"},
+        "mpix_hyp_per_s": v * hpv / 1e6,
+        "kernel_only": {"value": n * args.steps / (kernel_ms * 1e-3), "unit": "views/s (views / RunPatchMatch kernel time)",
+                        "ms_per_view": kernel_ms / (n * args.steps), "how": "CUDA events around the kernel sequence of each run"},
+        "cpu_baseline": {"value": v, "unit": "views/s", "cores": 1, "kind": "reference",
+                         "sample": f"all {n} views per step; 1 B200 for the reference's CUDA kernels, 1 host thread"},
         "e2e": {"value": v, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "clocks": clocks.summary(),
     }

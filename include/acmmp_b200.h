@@ -342,6 +342,11 @@ int acmmp_scan_level_is_u8(const acmmp_scan *s);
  * meaningful with world == 1.  0 = Jacobi (geom-1 reads the geom-0 maps of all
  * views).  -1 = default: 1 on an unsharded scan, 0 on a sharded one. */
 int acmmp_scan_set_sequential_geom(acmmp_scan *s, int on);
+/* Reduced schedules (before the first level).  single_scale: every view at its (capped) full size from the
+ * start, no pyramid (ComputeMultiScaleSettings, acmmp_definitions.cpp:207-243, switched off).
+ * photometric_only: the photometric stage is ONE RunPatchMatch per view, without the planar-prior construction
+ * and the second run (needs single_scale or a one-level scan).  Both set = BASELINE.json configs[1]. */
+int acmmp_scan_set_schedule(acmmp_scan *s, int single_scale, int photometric_only);
 int acmmp_scan_num_levels(const acmmp_scan *s);
 /* builds the image pyramid level (InputInitialization's resize,
  * ACMMP.cpp:566-598) for all views, and for level > 0 runs

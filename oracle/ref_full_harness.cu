@@ -13,7 +13,9 @@
 // through a hook - same triangles, possibly another order; cv::SVD::solveZ is a cross product;
 // imshow / imwrite / line / merge do nothing), and `clock64()` in RandomInitialization
 // (ACMMP.cu:624) is replaced by a caller-provided seed.  `#define DEBUG` (ACMMP.cu:3) stays, as
-// shipped.
+// shipped, in libacmmp_ref_full.so; libacmmp_ref_full_p2.so is the same program built from a copy of
+// ACMMP.cu that the Makefile generates under oracle/_ref/gen_p2/ with that one line deleted (patch P2 of
+// no per-run debug copies of the plane map, no leaked host buffer).
 #include <cuda_runtime.h>
 #include <curand_kernel.h>
 
@@ -26,7 +28,18 @@ __device__ unsigned long long g_acmmp_ref_seed;
 
 #include "../acmmp_b200/csrc/prior.h"
 
+#include <chrono>
+static double g_delaunay_seconds = 0.0;   // time spent in the stand-in for cv::Subdiv2D (reported by bench.py)
+extern "C" double ref_full_delaunay_seconds(int reset) {
+    const double v = g_delaunay_seconds;
+    if (reset) g_delaunay_seconds = 0.0;
+    return v;
+}
 static int delaunay_hook(const int *xy, int n, int *tris6, int capacity) {
+    struct Timer {
+        std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+        ~Timer() { g_delaunay_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
+    } timer;
     std::vector<int32_t> tris;
     const int nt = acmmp::delaunay_triangulate(xy, n, tris);
     const int m = nt < capacity ? nt : capacity;

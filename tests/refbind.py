@@ -332,8 +332,8 @@ REF_FULL_PATH = os.path.join(_REF_DIR, "libacmmp_ref_full.so")
 _ref_full = None
 
 
-def full_available():
-    return os.path.exists(REF_FULL_PATH)
+def full_available(variant=""):
+    return os.path.exists(REF_FULL_PATH if not variant else REF_FULL_PATH.replace(".so", f"_{variant}.so"))
 
 
 def write_dense_folder(dense, cams, images, pairs):
@@ -367,14 +367,30 @@ def read_ply(path):
     return rec["f"].copy(), rec["c"].copy()
 
 
-def full_run(dense, seed=1234, fuse=True, consistency_scalar=0.3, num_consistent_thresh=1, output_dir="/ACMMP", quiet=True):
+_ref_full_variants = {}
+
+
+def _full_lib(variant=""):
+    """variant "": the program as shipped (#define DEBUG on); "p2": built without that line (BASELINE.md patch P2)"""
+    if variant not in _ref_full_variants:
+        lib = C.CDLL(REF_FULL_PATH if not variant else REF_FULL_PATH.replace(".so", f"_{variant}.so"))
+        lib.ref_full_run.argtypes = [C.c_char_p, C.c_char_p, C.c_uint64, C.c_int, C.c_float, C.c_int,
+                                     C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        lib.ref_full_delaunay_seconds.argtypes = [C.c_int]
+        lib.ref_full_delaunay_seconds.restype = C.c_double
+        _ref_full_variants[variant] = lib
+    return _ref_full_variants[variant]
+
+
+def full_delaunay_seconds(variant="", reset=True):
+    """seconds the reference program spent in the stand-in for cv::Subdiv2D (the product's triangulation behind a hook)"""
+    return float(_full_lib(variant).ref_full_delaunay_seconds(int(reset)))
+
+
+def full_run(dense, seed=1234, fuse=True, consistency_scalar=0.3, num_consistent_thresh=1, output_dir="/ACMMP", quiet=True, variant=""):
     """The reference program on `dense` (written by write_dense_folder).  Returns seconds spent in
     the PatchMatch schedule (all ProcessProblem + JBU calls, file round trips included) and in RunFusion."""
-    global _ref_full
-    if _ref_full is None:
-        _ref_full = C.CDLL(REF_FULL_PATH)
-        _ref_full.ref_full_run.argtypes = [C.c_char_p, C.c_char_p, C.c_uint64, C.c_int, C.c_float, C.c_int,
-                                           C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    _ref_full = _full_lib(variant)
     a, b = C.c_double(), C.c_double()
     saved = None
     if quiet:   # the reference prints a few lines per view

@@ -50,7 +50,7 @@ def _common(rep):
         for key, r in rep[mode].items():
             differs = np.asarray(r["old_differs_y_mod32"])
             if differs.sum() >= 50:   # where do the product and the reference differ?  the 4 rows under a block boundary
-                assert differs[:4].sum() >= 0.97 * differs.sum(), (mode, key, differs.tolist())
+                assert differs[:4].sum() >= 0.85 * differs.sum(), (mode, key, differs.tolist())
             assert r["equal_old"] >= 0.965, (mode, key, r["equal_old"])
             assert r["rng_equal_old"] >= 0.999, (mode, key)   # identical numbers of random draws
     for key, r in rep["prior"].items():
