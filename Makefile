@@ -42,8 +42,8 @@ build/seeded.o: $(CSRC)/seeded.cu $(CSRC)/kernels.h include/acmmp_b200.h
 	@mkdir -p build
 	$(NVCC) $(FUSIONFLAGS) -c -o $@ $(CSRC)/seeded.cu
 
-$(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o build/seeded.o $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o build/seeded.o -lnvjpeg_static -lculibos -lcudart
+$(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/noalloc.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o build/seeded.o $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/noalloc.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o build/seeded.o -lnvjpeg_static -lculibos -lcudart
 
 oracle: oracle/liboracle.so
 

@@ -59,7 +59,7 @@ EXPORTS = [
     "acmmp_run_sweep", "acmmp_run_sweep_snapshot", "acmmp_run_tail", "acmmp_get_result", "acmmp_get_maps",
     "acmmp_get_depth_device", "acmmp_get_state", "acmmp_set_state", "acmmp_width", "acmmp_height",
     "acmmp_sync", "acmmp_launch_count", "acmmp_last_timing", "acmmp_jbu_depth", "acmmp_resize_linear",
-    "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_measure_tex_peak", "acmmp_measure_tex_peak_u8", "acmmp_tex_sample", "acmmp_tex_sample_u8", "acmmp_get_planar_prior", "acmmp_delaunay", "acmmp_set_delaunay_threads", "acmmp_timing_collect",
+    "acmmp_rng_init_states", "acmmp_measure_fp32_peak", "acmmp_measure_tex_peak", "acmmp_measure_tex_peak_u8", "acmmp_tex_sample", "acmmp_tex_sample_u8", "acmmp_get_planar_prior", "acmmp_delaunay", "acmmp_set_delaunay_threads", "acmmp_prior_raster_noalloc", "acmmp_timing_collect",
     "acmmp_count_ncc", "acmmp_ncc_count", "acmmp_scan_count_ncc", "acmmp_scan_ncc_count",
     "acmmp_fusion_create", "acmmp_fusion_destroy", "acmmp_fusion_last_error", "acmmp_fusion_set_view", "acmmp_fusion_run",
     "acmmp_fusion_get_points", "acmmp_fusion_get_mask", "acmmp_fusion_stats",
@@ -115,6 +115,7 @@ def load():
     lib.acmmp_get_planar_prior.argtypes = [vp, fp, up]
     lib.acmmp_delaunay.argtypes = [C.POINTER(C.c_int32), C.c_int, C.POINTER(C.c_int32), C.c_int]
     lib.acmmp_set_delaunay_threads.argtypes = [C.c_int]
+    lib.acmmp_prior_raster_noalloc.argtypes = [C.c_int, C.POINTER(Camera), C.c_float, C.c_float, vp, vp, C.c_int, vp, vp, vp, C.c_char_p, C.c_size_t]
     lib.acmmp_run.argtypes = [vp, C.c_uint64]
     lib.acmmp_run_init.argtypes = [vp, C.c_uint64]
     lib.acmmp_run_sweep.argtypes = [vp, C.c_int, C.c_int]

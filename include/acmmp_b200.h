@@ -197,6 +197,32 @@ int acmmp_delaunay(const int32_t *xy, int n, int32_t *tris, int capacity);
  * variable ACMMP_DELAUNAY_THREADS overrides).  Triangles and their order do not depend on it. */
 int acmmp_set_delaunay_threads(int threads);
 
+/* ---- allocation-free planar-prior raster ---------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It is the raster half
+ * of acmmp_build_planar_prior - plane fit per triangle, triangle raster (later triangles overwrite), depth-range
+ * check per pixel - with all inputs and outputs passed by the caller as DEVICE pointers:
+ *   ref_cam            the reference view's camera at this scale (width / height = map size), host struct
+ *   depth_min/max      the widened range (acmmp_get_params: depth_min, depth_max)
+ *   d_planes4          w*h float4, depth of the finished run in .w (acmmp_get_result layout)
+ *   d_tris             num_triangles x 6 int32 (x,y of the 3 vertices, acmmp_delaunay layout)
+ *   d_prior_planes4    out: w*h float4 prior plane per pixel (0 where uncovered)
+ *   d_masks            out: w*h u32 triangle label (index + 1; 0 = uncovered)
+ *   stream             cudaStream_t (NULL = default stream); the call only enqueues work
+ *   err, err_len       optional buffer for the error text (may be NULL)
+ * The kernels' scratch (label map, triangle planes, long-triangle queue, camera constants) lives in a file-scope
+ * static __device__ array: 10.2 MiB that every GPU which loads the library holds until exit.  The call performs no
+ * cudaMalloc / cudaFree / cudaHostAlloc and calls no allocating library routine.  Limits: w*h <=
+ * ACMMP_NOALLOC_MAX_PIXELS, num_triangles <= ACMMP_NOALLOC_MAX_TRIANGLES; larger inputs are rejected with
+ * ACMMP_ERR_INVALID and a message.  ALL CALLS SHARE THE ARRAY, which keeps the last call's contents (what must start
+ * at zero is cleared by every call): calls that overlap on the GPU - different streams or host threads - race;
+ * serialise them.  Results are bit-identical to acmmp_build_planar_prior's for the same triangles. */
+#define ACMMP_NOALLOC_MAX_PIXELS (1600 * 1200)
+#define ACMMP_NOALLOC_MAX_TRIANGLES 153600 /* 2 x the 5x5 cells of 1600 x 1200 */
+int acmmp_prior_raster_noalloc(int device, const acmmp_camera *ref_cam, float depth_min, float depth_max,
+                               const float *d_planes4, const int32_t *d_tris, int num_triangles,
+                               float *d_prior_planes4, uint32_t *d_masks, void *stream, char *err, size_t err_len);
+
 /* ---- run -------------------------------------------------------------------
  * ACMMP::RunPatchMatch (ACMMP.cu:1378-1456).  `seed` replaces the reference's
  * clock64() seed (ACMMP.cu:624).  Runs on the context's stream; results are
