@@ -19,11 +19,14 @@ REF_CXX   ?= $(shell command -v g++)
 all: $(LIB) oracle cli
 
 # command line with the reference's flags and file layout (cli/acmmp_main.cpp) over the C ABI
-cli: build/acmmp_main build/io_selftest
+cli: build/acmmp_main build/fuse_data build/io_selftest
 build/io_selftest: cli/io_selftest.cpp $(wildcard acmmp_b200/host/*.hpp) include/acmmp_b200.h
 	@mkdir -p build
 	$(REF_CXX) -O2 -std=c++17 -Wall -o $@ cli/io_selftest.cpp -lz
-build/acmmp_main: cli/acmmp_main.cpp $(wildcard acmmp_b200/host/*.hpp) include/acmmp_b200.h $(LIB)
+build/fuse_data: cli/fuse_data.cpp cli/fuse_common.hpp $(wildcard acmmp_b200/host/*.hpp) include/acmmp_b200.h $(LIB)
+	@mkdir -p build
+	$(REF_CXX) -O2 -std=c++17 -Wall -o $@ cli/fuse_data.cpp -Lacmmp_b200 -lacmmp_b200 -Wl,-rpath,'$$ORIGIN/../acmmp_b200' -L$(CUDA_LIB) -lcudart -lz
+build/acmmp_main: cli/acmmp_main.cpp cli/fuse_common.hpp $(wildcard acmmp_b200/host/*.hpp) include/acmmp_b200.h $(LIB)
 	@mkdir -p build
 	$(REF_CXX) -O2 -std=c++17 -Wall -o $@ cli/acmmp_main.cpp -Lacmmp_b200 -lacmmp_b200 -Wl,-rpath,'$$ORIGIN/../acmmp_b200' -L$(CUDA_LIB) -lcudart -lz
 
@@ -52,7 +55,7 @@ oracle/liboracle.so: $(wildcard oracle/*.c) $(wildcard oracle/*.h)
 
 # The reference's own kernels, compiled from where they lie (never copied into the
 # repo), sm_100 + the reference's flags; only built where /root/reference exists.
-ref: oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so oracle/_ref/libacmmp_ref_full_p2.so
+ref: oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so oracle/_ref/libacmmp_ref_full_p2.so oracle/_ref/libacmmp_dropin.so
 oracle/_ref/libacmmp_ref.so: oracle/ref_harness.cu $(wildcard oracle/ref_stub/opencv2/*.hpp)
 	@if [ -d $(REF) ]; then mkdir -p oracle/_ref && \
 	$(NVCC) -O3 --use_fast_math --maxrregcount=128 -std=c++14 -gencode arch=compute_100,code=sm_100 \
@@ -79,6 +82,15 @@ oracle/_ref/libacmmp_ref_full_p2.so: oracle/ref_full_harness.cu acmmp_b200/csrc/
 	rc=$$?; rm -rf oracle/_ref/gen_p2; exit $$rc; \
 	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
 
+# The drop-in proof: the reference's UNCHANGED ACMMP.h + acmmp_definitions.cpp on top of
+# oracle/dropin/ACMMP_dropin.cpp (class ACMMP / RunJBU / helpers over the C ABI) instead of its ACMMP.cpp / ACMMP.cu.
+dropin: oracle/_ref/libacmmp_dropin.so
+oracle/_ref/libacmmp_dropin.so: oracle/dropin/ACMMP_dropin.cpp oracle/dropin/dropin_main.cpp include/acmmp_b200.h $(LIB) $(wildcard oracle/ref_stub/opencv2/*.hpp)
+	@if [ -d $(REF) ]; then mkdir -p oracle/_ref && \
+	$(REF_CXX) -O2 -std=c++14 -fPIC -shared -w -Ioracle/ref_stub -I$(REF) -Iinclude -I$(CUDA_INC) -o $@ oracle/dropin/ACMMP_dropin.cpp oracle/dropin/dropin_main.cpp \
+	  -Lacmmp_b200 -lacmmp_b200 -Wl,-rpath,'$$ORIGIN/../../acmmp_b200' -L$(CUDA_LIB) -lcudart ; \
+	else echo "reference sources absent: keeping prebuilt oracle/_ref"; fi
+
 # The reference's HOST code (RunFusion + helpers: ACMMP.cpp, acmmp_definitions.cpp) against the
 # stand-in OpenCV.  Two builds: the reference's own flags (src/CMakeLists.txt:28, minus
 # -march=native so that the library also runs on the GPU box's CPU) and plain IEEE arithmetic
@@ -95,4 +107,4 @@ oracle/_ref/libacmmp_ref_host_ieee.so: $(REF_HOST_SRC)
 
 clean:
 	rm -f $(LIB) build/fusion.o build/pairs.o build/seeded.o oracle/liboracle.so oracle/_ref/libacmmp_ref.so oracle/_ref/libacmmp_ref_host.so oracle/_ref/libacmmp_ref_host_ieee.so oracle/_ref/libacmmp_ref_full.so oracle/_ref/libacmmp_ref_full_p2.so
-.PHONY: all oracle ref cli clean
+.PHONY: all oracle ref cli clean dropin

@@ -90,6 +90,7 @@ struct acmmp_ctx {
     std::string error;
     acmmp_params params;
     int compat = ACMMP_COMPAT_REF_SM100;
+    int split = -1;        // half-finished ping-pong pair: colour whose newest pixels sit in planes_snap (capi_run.cu.inc)
     int wave_blocks = 0;   // acmmp_set_wave_emulation: resident blocks of the reference launch (0 = off)
     int n = 0;   // images in the problem
     int W = 0, H = 0;

@@ -355,6 +355,7 @@ cudaError_t launch_init(const InitLaunch &L, cudaStream_t st) {
 
 cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st) {
     SweepArgs a;
+    a.planes_other = L.planes_other; a.costs_other = L.costs_other;
     a.planes_in = L.planes_in; a.costs_in = L.costs_in; a.planes_self = L.planes_self; a.costs_self = L.costs_self;
     a.planes = L.planes; a.costs = L.costs;
     a.selected_views = L.selected_views; a.pre_costs = L.pre_costs; a.prior_planes = L.prior_planes;
@@ -374,6 +375,21 @@ cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st) {
     }
     if (L.tex_u8) sweep_kernel<true><<<grid2(L.W, L.H, kTileW, kTileH), kSweepThreads, smem, st>>>(a);
     else sweep_kernel<false><<<grid2(L.W, L.H, kTileW, kTileH), kSweepThreads, smem, st>>>(a);
+    return cudaGetLastError();
+}
+
+__global__ void merge_color_kernel(float4 *__restrict__ planes_dst, float *__restrict__ costs_dst, const float4 *__restrict__ planes_src,
+                                   const float *__restrict__ costs_src, int W, int H, int color) {
+    const int y = blockIdx.y * blockDim.y + threadIdx.y;
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((y + color) & 1);
+    if (x >= W || y >= H) return;
+    const int c = y * W + x;
+    planes_dst[c] = planes_src[c];
+    costs_dst[c] = costs_src[c];
+}
+cudaError_t launch_merge_color(float4 *planes_dst, float *costs_dst, const float4 *planes_src, const float *costs_src, int W, int H, int color,
+                               cudaStream_t st) {
+    merge_color_kernel<<<grid2((W + 1) / 2, H, 32, 8), dim3(32, 8), 0, st>>>(planes_dst, costs_dst, planes_src, costs_src, W, H, color);
     return cudaGetLastError();
 }
 

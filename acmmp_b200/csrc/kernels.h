@@ -30,6 +30,8 @@ struct InitLaunch {
 };
 
 struct SweepLaunch {
+    const float4 *planes_other;
+    const float *costs_other;
     const float4 *planes_in;
     const float *costs_in;
     const float4 *planes_self;
@@ -59,6 +61,9 @@ cudaError_t launch_setup_pairs(const acmmp_camera *h_cams, int n, const float *c
 cudaError_t launch_rng_init(unsigned long long seed, int W, int H, uint32_t *d_rng6, cudaStream_t st);
 cudaError_t launch_init(const InitLaunch &L, cudaStream_t st);
 cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st);
+// pixels of `color` ((x + y) & 1) of src -> dst (planes and costs): merges a half-finished ping-pong pair
+cudaError_t launch_merge_color(float4 *planes_dst, float *costs_dst, const float4 *planes_src, const float *costs_src, int W, int H, int color,
+                               cudaStream_t st);
 cudaError_t launch_depth_normal(float4 *planes, const RefConst *rc, int W, int H, cudaStream_t st);
 cudaError_t launch_median_filter(float4 *planes, const float *costs, int W, int H, int color, cudaStream_t st);
 cudaError_t launch_split_maps(const float4 *planes, int n, float *depth, float *normal3, cudaStream_t st);

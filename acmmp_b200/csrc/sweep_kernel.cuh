@@ -24,10 +24,9 @@
 //    group carries an identical copy, so all lanes make the same draws).
 //  * same-colour reads (the V-shaped near-arm candidates sit on the colour
 //    being rewritten, a data race in the reference) see the state before the
-//    launch: planes / costs are ping-pong buffers (read one, write the other,
-//    the other colour's pixels are copied across by the same CTA), which is
-//    deterministic and what the reference does whenever the neighbour has not
-//    finished yet.
+//    launch: planes / costs are ping-pong buffers (SweepArgs: read one, write
+//    the other, no copies), which is deterministic and what the reference does
+//    whenever the neighbour has not finished yet.
 #pragma once
 #include "common.cuh"
 #include "geometry.cuh"
@@ -48,14 +47,18 @@ constexpr int kInitGroups = kInitTileW * kInitTileH;   // pixels per CTA
 constexpr int kInitThreads = kInitGroup * kInitGroups;
 
 struct SweepArgs {
-    // State before the half-sweep (read) and after it (write).  Production: ping-pong - `planes_in` ==
-    // `planes_self` is the state before, `planes` the other buffer; the kernel writes its colour's pixels
-    // and copies the other colour's across, so no snapshot copy is needed.  Diagnostics
-    // (acmmp_run_sweep_snapshot): neighbour reads from an injected snapshot, centre from the live state,
-    // written in place (`planes` == `planes_self`).
-    const float4 *planes_in;     // neighbour planes (candidates of the 8 arms)
-    const float *costs_in;       // neighbour costs
-    const float4 *planes_self;   // the pixel's own plane; source of the other colour's copy
+    // State before the half-sweep (read) and after it (write): a ping-pong pair X / Y without copies.  The black and
+    // the red half-sweep of an iteration form a pair: the first reads everything from X and writes its colour to Y;
+    // the second reads the OTHER colour (odd Manhattan distance: direct neighbours, far arms) from Y - the values the
+    // first just wrote - and its own colour (the V candidates, its own plane) from X, and writes to Y, which then
+    // holds the whole state.  Same-colour reads therefore always see the state before the launch.
+    // Diagnostics (acmmp_run_sweep_snapshot): all neighbour reads from an injected snapshot, own plane from the live
+    // state, written in place.
+    const float4 *planes_other;  // planes / costs of the other colour
+    const float *costs_other;
+    const float4 *planes_in;     // planes / costs of the same colour before this half-sweep
+    const float *costs_in;
+    const float4 *planes_self;   // the pixel's own plane
     const float *costs_self;
     float4 *planes;
     float *costs;

@@ -71,6 +71,7 @@ def parse_args():
                     help="auto: R8 unorm texels on levels that are not resized (bit-identical samples); r32f: float texels everywhere")
     ap.add_argument("--ref-views", type=int, default=4, help="views of the reference arm's kernel-only pass (bounded sample)")
     ap.add_argument("--ref-full-scan", action="store_true", help="reference arm: every view of the scan per step instead of the bounded sub-scan")
+    ap.add_argument("--ref-kernel-only-child", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--no-ref-p2", action="store_true", help="reference arm: skip the extra step with patch P2 (#define DEBUG removed)")
     args = ap.parse_args()
     preset = CONFIGS[args.config]
@@ -552,6 +553,11 @@ def run_reference(args):
         return
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import refbind
+    if args.ref_kernel_only_child:
+        import torch
+        torch.cuda.set_device(0)
+        print(json.dumps(reference_kernel_only(args, make_scan_inputs(args, torch.device("cuda", 0)))), flush=True)
+        return
     if args.config == "photometric":
         return run_reference_photometric(args)
     if not refbind.full_available():
@@ -601,7 +607,14 @@ def run_reference(args):
     v = len(sample) * args.steps / t_pm
     kernel_only = None
     if args.config == "full" and refbind.available():
-        kernel_only = reference_kernel_only(args, sc)
+        # in a process of its own: libacmmp_ref.so and libacmmp_ref_full.so both define the reference's kernels (same
+        # symbols), and the dynamic linker would bind the second library's launches to the first one's stubs
+        cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--ref-kernel-only-child", "--config", args.config,
+               "--views", str(args.views), "--width", str(args.width), "--height", str(args.height), "--nsrc", str(args.nsrc),
+               "--seed", str(args.seed), "--ref-views", str(args.ref_views)]
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=1200)
+        lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+        kernel_only = json.loads(lines[-1]) if (out.returncode == 0 and lines) else {"unavailable": (out.stderr or "no output")[-300:]}
     line = {
         "impl": "reference",
         "metric": CONFIGS[args.config]["metric"],

@@ -17,51 +17,10 @@
 #include <string>
 #include <vector>
 
-#define ACMMP_IO_WITH_JPEG 1
-#define ACMMP_IO_WITH_PNG 1
-#include "../acmmp_b200/host/acmmp.hpp"
+#include "fuse_common.hpp"
 
 using namespace acmmp_b200;
-
-static std::string id_name(int id, const char *suffix) {
-    char buf[64];
-    snprintf(buf, sizeof buf, "%08d%s", id, suffix);
-    return buf;
-}
-
-static bool find_image(const std::string &folder, int id, Map<uint8_t> &im, std::string &err, bool color, int device) {
-    for (const char *ext : {".jpg", ".pgm", ".ppm", ".raw"}) {   // the parity tests keep the reference's .jpg name for the raw container
-        std::string e;
-        if (ReadImage(folder + "/" + id_name(id, ext), im, &e, color, device)) return true;
-        if (!e.empty() && e.find("cannot open") == std::string::npos) err = e;
-    }
-    if (err.empty()) err = "no image for id " + std::to_string(id) + " under " + folder;
-    return false;
-}
-
-// <dense>/<mask_dir>/%08d.png as cv::imread(path, -1) returns it (acmmp_definitions.cpp:886-895), first channel, as bytes;
-// 16-bit samples are clamped to 255 (only `< 128` is asked of them).  PGM / raw containers are accepted too.
-static bool find_mask(const std::string &folder, int id, Map<uint8_t> &m, std::string &err, int device) {
-    Map<uint16_t> png;
-    std::string e;
-    if (ReadPng16(folder + "/" + id_name(id, ".png"), png, nullptr, &e)) {
-        m = Map<uint8_t>(png.rows, png.cols, 1);
-        for (size_t k = 0; k < (size_t)png.rows * png.cols; ++k) {
-            const uint16_t v = png.data[k * png.channels];
-            m.data[k] = (uint8_t)(v > 255 ? 255 : v);
-        }
-        return true;
-    }
-    if (e.find("cannot open") == std::string::npos) {
-        err = e;
-        return false;
-    }
-    Map<uint8_t> any;
-    if (!find_image(folder, id, any, err, false, device)) return false;
-    m = Map<uint8_t>(any.rows, any.cols, 1);
-    for (size_t k = 0; k < (size_t)any.rows * any.cols; ++k) m.data[k] = any.data[k * any.channels];
-    return true;
-}
+using namespace acmmp_cli;
 
 int main(int argc, char **argv) {
     std::string dense_folder, output_dir = "/ACMMP", mask_dir = " ", image_dir = "/images";
@@ -192,78 +151,27 @@ int main(int argc, char **argv) {
                 fprintf(stderr, "cannot write maps under %s\n", folder.c_str());
                 return EXIT_FAILURE;
             }
-            // RescaleImageAndCamera (ACMMP.cpp:179-203): camera at the size of the depth map
-            cams_out[i] = cams[i];
-            const float sx = depth.cols / (float)cams[i].width, sy = depth.rows / (float)cams[i].height;
-            if (depth.cols != cams[i].width || depth.rows != cams[i].height) {
-                cams_out[i].K[0] *= sx; cams_out[i].K[2] *= sx; cams_out[i].K[4] *= sy; cams_out[i].K[5] *= sy;
-                cams_out[i].width = depth.cols;
-                cams_out[i].height = depth.rows;
-            }
+            cams_out[i] = CameraAtMapSize(cams[i], depth.cols, depth.rows);
         }
         printf("depth maps written to %s\n", output_folder.c_str());
         if (fuse) {
-            const bool prior_aware = (prior && multi_fusion) || force_fusion;   // main_ACMMP.cpp:181
-            const std::string fusion_folder = dense_folder + fusion_dir;
-            Fusion fusion(cams_out, pairs, device);
-            for (int i = 0; i < n; ++i) {
-                Map<uint8_t> color;   // colour read for the point colours (acmmp_definitions.cpp:857)
-                {
-                    std::string err;
-                    if (!find_image(dense_folder + image_dir, problems[i].ref_image_id, color, err, true, device)) {
-                        fprintf(stderr, "%s\n", err.c_str());
-                        return EXIT_FAILURE;
-                    }
-                }
-                if (color.channels == 1) {   // grey input: replicate like imread(IMREAD_COLOR)
-                    Map<uint8_t> c3(color.rows, color.cols, 3);
-                    for (size_t k = 0; k < (size_t)color.rows * color.cols; ++k) c3.data[3 * k] = c3.data[3 * k + 1] = c3.data[3 * k + 2] = color.data[k];
-                    color = c3;
-                }
-                // RescaleImageAndCamera (ACMMP.cpp:179-203): the colour image at the size of the depth map
-                if (color.cols != cams_out[i].width || color.rows != cams_out[i].height) color = ResizeLinear8(color, cams_out[i].width, cams_out[i].height);
-                std::vector<uint8_t> mask;
-                if (mask_dir != " ") {   // acmmp_definitions.cpp:884-899: %08d.png, resized to the depth map, mask = value < 128
-                    Map<uint8_t> m;
-                    std::string err;
-                    if (!find_mask(dense_folder + "/" + mask_dir, problems[i].ref_image_id, m, err, device)) {
-                        fprintf(stderr, "mask of image %d: %s\n", problems[i].ref_image_id, err.c_str());
-                        return EXIT_FAILURE;
-                    }
-                    if (m.cols != cams_out[i].width || m.rows != cams_out[i].height) m = ResizeLinear8(m, cams_out[i].width, cams_out[i].height);
-                    mask.resize((size_t)m.rows * m.cols);
-                    for (size_t k = 0; k < mask.size(); ++k) mask[k] = m.data[k] < 128 ? 1 : 0;
-                }
-                // colour and mask come from the host, so the maps take the same way (one flag per call)
-                Map<float> hd, hn;
-                scan.GetView(i, &hd, &hn, nullptr);
-                if (prior_aware) {
-                    // set 0 = the maps of the fusion folder, set 1 = this run's (acmmp_definitions.cpp:607-643)
-                    const std::string folder = fusion_folder + "/2333_" + id_name(problems[i].ref_image_id, "");
-                    Map<float> d0, n0;
-                    if (readDepthDmb(folder + "/depths_geom.dmb", d0) || readNormalDmb(folder + "/normals.dmb", n0) ||
-                        d0.cols != cams_out[i].width || d0.rows != cams_out[i].height) {
-                        fprintf(stderr, "cannot read the maps of image %d under %s\n", problems[i].ref_image_id, folder.c_str());
-                        return EXIT_FAILURE;
-                    }
-                    fusion.SetView(i, d0.data.data(), n0.data.data(), color.data.data(), mask.empty() ? nullptr : mask.data(), false);
-                    fusion.SetViewSecond(i, hd.data.data(), hn.data.data(), false);
-                } else {
-                    fusion.SetView(i, hd.data.data(), hn.data.data(), color.data.data(), mask.empty() ? nullptr : mask.data(), false);
-                }
-            }
-            const int64_t count = prior_aware ? fusion.RunPriorAware(consistency_scalar, num_consistent_thresh, single_match_penalty)
-                                              : fusion.Run(consistency_scalar, num_consistent_thresh);
-            std::vector<float> pts;
-            std::vector<int64_t> per_view;
-            fusion.GetPoints(pts, per_view, count, n);
-            for (int i = 0; i < n; ++i) printf("Fusing image %08d... approved %lld pts\n", i, (long long)per_view[i]);
-            if (!StoreColorPlyFileBinaryPointCloud(output_folder + (prior_aware ? "/ACMMP_prior_model.ply" : "/ACMMP_model.ply"), pts.data(),
-                                                   (size_t)count)) {
-                fprintf(stderr, "cannot write the PLY\n");
+            FuseOptions o;
+            o.dense_folder = dense_folder;
+            o.output_folder = output_folder;
+            o.fusion_folder = dense_folder + fusion_dir;
+            o.image_dir = image_dir;
+            o.mask_dir = mask_dir;
+            o.prior_aware = (prior && multi_fusion) || force_fusion;   // main_ACMMP.cpp:181
+            o.consistency_scalar = consistency_scalar;
+            o.num_consistent_thresh = num_consistent_thresh;
+            o.single_match_penalty = single_match_penalty;
+            o.device = device;
+            // colour and mask come from the host, so the maps take the same way (one flag per call)
+            if (FuseAndStore(o, problems, cams_out, pairs, [&](int i, Map<float> &d, Map<float> &nrm) {
+                    scan.GetView(i, &d, &nrm, nullptr);
+                    return true;
+                }) < 0)
                 return EXIT_FAILURE;
-            }
-            printf("store 3D points to ply file: %lld points\n", (long long)count);
         }
     } catch (const std::exception &e) {
         fprintf(stderr, "%s\n", e.what());   // the reference: CudaSafeCall prints and exit(EXIT_FAILURE)

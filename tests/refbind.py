@@ -409,3 +409,35 @@ def full_run(dense, seed=1234, fuse=True, consistency_scalar=0.3, num_consistent
             os.close(saved)
     assert rc == 0
     return a.value, b.value
+
+
+# ---- the drop-in proof: the reference's unchanged ACMMP.h + acmmp_definitions.cpp over libacmmp_b200.so --------------
+DROPIN_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle", "_ref", "libacmmp_dropin.so")
+_dropin = None
+
+
+def dropin_available():
+    return os.path.exists(DROPIN_PATH)
+
+
+def dropin_run(dense, seed=1234, fuse=True, consistency_scalar=0.3, num_consistent_thresh=1, output_dir="/ACMMP", quiet=True):
+    """main() of the reference on top of oracle/dropin/ACMMP_dropin.cpp (class ACMMP over the C ABI)"""
+    global _dropin
+    if _dropin is None:
+        _dropin = C.CDLL(DROPIN_PATH)
+        _dropin.dropin_run.argtypes = [C.c_char_p, C.c_char_p, C.c_uint64, C.c_int, C.c_float, C.c_int]
+    saved = None
+    if quiet:
+        import sys
+        sys.stdout.flush()
+        saved = os.dup(1)
+        devnull = os.open(os.devnull, os.O_WRONLY)
+        os.dup2(devnull, 1)
+        os.close(devnull)
+    try:
+        rc = _dropin.dropin_run(dense.encode(), output_dir.encode(), seed, int(fuse), consistency_scalar, num_consistent_thresh)
+    finally:
+        if saved is not None:
+            os.dup2(saved, 1)
+            os.close(saved)
+    assert rc == 0

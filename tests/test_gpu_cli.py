@@ -246,3 +246,42 @@ def test_cli_reads_png_masks_in_the_reference_format(cli_run):
     os.remove(os.path.join(dense, "masks", "%08d.png" % ids[0]))
     out = subprocess.run([EXE, dense, "--seed", "5", "--output_dir", "/MASKED", "--mask_dir", "masks"], capture_output=True, text=True)
     assert out.returncode != 0 and "mask of image" in out.stderr
+
+
+@pytest.mark.skipif(not refbind.host_available(), reason="oracle/_ref/libacmmp_ref_host*.so not built")
+def test_fuse_data_refuses_the_output_folder_like_the_reference(cli_run):
+    """build/fuse_data = main_fusion.cpp: re-fuses <dense>/ACMMP from depths.dmb (geom_consistency = false there,
+    main_fusion.cpp:75) + normals.dmb; the reference's own RunFusion with the same flag reads the same folder."""
+    exe = os.path.join(ROOT, "build", "fuse_data")
+    if not os.path.exists(exe):
+        pytest.skip("build/fuse_data not built (make cli)")
+    sc, dense, ids, _ = cli_run
+    n = len(ids)
+    outdir = os.path.join(dense, "ACMMP")
+    out = subprocess.run([exe, dense, "-f", "0.3", "--num_consistent_thresh", "2"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    assert "approved" in out.stdout
+    xyz_n, col = read_ply(os.path.join(outdir, "ACMMP_model.ply"))
+    shutil.copy(os.path.join(outdir, "ACMMP_model.ply"), os.path.join(outdir, "fuse_data.ply"))
+    import ctypes as C
+    lib = C.CDLL(refbind.REF_HOST_PATHS["ieee"])
+    lib.ref_host_run_fusion.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                        C.c_int, C.c_float, C.c_int]
+    offs, flat = [0], []
+    for p in sc["pairs"]:
+        flat += [ids[j] for j in p]
+        offs.append(len(flat))
+    rc = lib.ref_host_run_fusion(dense.encode(), outdir.encode(), n, (C.c_int * n)(*ids), (C.c_int * (n + 1))(*offs),
+                                 (C.c_int * len(flat))(*flat), 0, 0.3, 2)
+    assert rc == 0
+    ref_xyz_n, ref_col = read_ply(os.path.join(outdir, "ACMMP_model.ply"))
+    assert len(ref_xyz_n) > 20000
+    assert abs(len(ref_xyz_n) - len(xyz_n)) <= max(1, int(1e-3 * len(ref_xyz_n))), (len(ref_xyz_n), len(xyz_n))
+    if len(ref_xyz_n) == len(xyz_n):
+        assert (ref_xyz_n.view(np.uint32) == xyz_n.view(np.uint32)).all(1).mean() >= 0.999
+        assert (ref_col == col).all()
+    # a missing map is an error
+    os.rename(os.path.join(outdir, "2333_%08d" % ids[1], "normals.dmb"), os.path.join(outdir, "2333_%08d" % ids[1], "normals.bak"))
+    out = subprocess.run([exe, dense], capture_output=True, text=True)
+    os.rename(os.path.join(outdir, "2333_%08d" % ids[1], "normals.bak"), os.path.join(outdir, "2333_%08d" % ids[1], "normals.dmb"))
+    assert out.returncode != 0 and "cannot read the maps" in out.stderr
