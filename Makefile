@@ -28,7 +28,7 @@ build/fuse_data: cli/fuse_data.cpp cli/fuse_common.hpp $(wildcard acmmp_b200/hos
 	$(REF_CXX) -O2 -std=c++17 -Wall -o $@ cli/fuse_data.cpp -Lacmmp_b200 -lacmmp_b200 -Wl,-rpath,'$$ORIGIN/../acmmp_b200' -L$(CUDA_LIB) -lcudart -lz
 build/acmmp_main: cli/acmmp_main.cpp cli/fuse_common.hpp $(wildcard acmmp_b200/host/*.hpp) include/acmmp_b200.h $(LIB)
 	@mkdir -p build
-	$(REF_CXX) -O2 -std=c++17 -Wall -o $@ cli/acmmp_main.cpp -Lacmmp_b200 -lacmmp_b200 -Wl,-rpath,'$$ORIGIN/../acmmp_b200' -L$(CUDA_LIB) -lcudart -lz
+	$(REF_CXX) -O2 -std=c++17 -Wall -pthread -o $@ cli/acmmp_main.cpp -Lacmmp_b200 -lacmmp_b200 -Wl,-rpath,'$$ORIGIN/../acmmp_b200' -L$(CUDA_LIB) -lcudart -lz
 
 # fusion.cu restates host code of the reference (IEEE float / double): no fast math, no contraction
 FUSIONFLAGS := -O3 -std=c++17 $(ARCH) -lineinfo -fmad=false -Xcompiler -fPIC
@@ -46,7 +46,7 @@ build/seeded.o: $(CSRC)/seeded.cu $(CSRC)/kernels.h include/acmmp_b200.h
 	$(NVCC) $(FUSIONFLAGS) -c -o $@ $(CSRC)/seeded.cu
 
 $(LIB): $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/noalloc.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o build/seeded.o $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.inc) $(wildcard $(CSRC)/*.h) include/acmmp_b200.h
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/noalloc.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o build/seeded.o -lnvjpeg_static -lculibos -lcudart
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/kernels.cu $(CSRC)/capi.cu $(CSRC)/noalloc.cu $(CSRC)/prior.cpp $(CSRC)/jpeg.cpp build/fusion.o build/pairs.o build/seeded.o -lnvjpeg_static -lculibos -lcudart -ldl
 
 oracle: oracle/liboracle.so
 

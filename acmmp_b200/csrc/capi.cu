@@ -658,3 +658,4 @@ int acmmp_set_planar_prior(acmmp_ctx *ctx, const float *planes4, const uint32_t 
 
 #include "capi_run.cu.inc"
 #include "capi_scan.cu.inc"
+#include "capi_nccl.cu.inc"

@@ -312,6 +312,19 @@ def measure_tex_peak(device=0, u8=False):
 STAGE_PHOTO, STAGE_GEOM0, STAGE_GEOM1 = 0, 1, 2
 
 
+def nccl_version():
+    return int(L.load().acmmp_nccl_version())
+
+
+def nccl_unique_id():
+    """128 bytes to hand to every rank's Scan.comm_init (rank 0 calls this)"""
+    buf = (C.c_uint8 * 128)()
+    rc = L.load().acmmp_nccl_get_unique_id(buf)
+    if rc != 0:
+        raise L.AcmmpError(f"acmmp_nccl_get_unique_id failed ({rc}): {L.load().acmmp_last_error(None).decode()}")
+    return bytes(buf)
+
+
 class Scan:
     """The stage graph of the reference's main() (main_ACMMP.cpp:89-176) over a set of
     views with all data resident on the device; `exchange` is called after every
@@ -382,6 +395,20 @@ class Scan:
 
     def num_levels(self):
         return self._lib.acmmp_scan_num_levels(self._s)
+
+    # ---- multi-GPU: NCCL inside the library (include/acmmp_b200.h) ---------------------------------------------
+    def comm_init(self, unique_id):
+        """collective over the world given at construction; unique_id: the 128 bytes of nccl_unique_id() of rank 0"""
+        buf = (C.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
+        self._ck(self._lib.acmmp_scan_comm_init(self._s, buf), "comm_init")
+
+    def all_gather(self):
+        """depth maps of the owned views -> every rank, on the scan's stream (no host sync); no-op when unsharded"""
+        self._ck(self._lib.acmmp_scan_all_gather(self._s), "all_gather")
+
+    def collect_view(self, view, root, d_normal3=None, d_cost=None):
+        """owner -> root: normals + costs of `view` into the root's device buffers (int pointers)"""
+        self._ck(self._lib.acmmp_scan_collect_view(self._s, view, root, C.c_void_p(d_normal3), C.c_void_p(d_cost)), "collect_view")
 
     def set_sequential_geom(self, on):
         """geom-1 order: True = the reference's in-place order, False = Jacobi, None = the default (in place when unsharded)"""

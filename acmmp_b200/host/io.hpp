@@ -32,9 +32,32 @@ template <class T> struct Map {
     const T &at(int r, int c, int k = 0) const { return data[((size_t)r * cols + c) * channels + k]; }
 };
 
-struct Problem {   // acmmp_definitions.h:57-65
+struct Problem {   // acmmp_definitions.h:57-63
     int ref_image_id = 0;
     std::vector<int> src_image_ids;
+    int max_image_size = 6400;
+    int num_downscale = 0;
+    int cur_image_size = 6400;
+};
+
+// stand-ins for the cv:: / CUDA vector types in the reference's signatures (ACMMP.h:60-89, acmmp_definitions.h:65-68)
+struct Point2i {   // cv::Point
+    int x = 0, y = 0;
+    Point2i() {}
+    Point2i(int x_, int y_) : x(x_), y(y_) {}
+};
+struct Rect {   // cv::Rect
+    int x = 0, y = 0, width = 0, height = 0;
+    Rect() {}
+    Rect(int x_, int y_, int w_, int h_) : x(x_), y(y_), width(w_), height(h_) {}
+    bool contains(const Point2i &p) const { return p.x >= x && p.x < x + width && p.y >= y && p.y < y + height; }
+};
+struct Triangle {   // acmmp_definitions.h:65-68
+    Point2i pt1, pt2, pt3;
+    Triangle(const Point2i &a, const Point2i &b, const Point2i &c) : pt1(a), pt2(b), pt3(c) {}
+};
+struct Float4 {   // CUDA's float4: plane hypothesis (nx, ny, nz, d)
+    float x = 0, y = 0, z = 0, w = 0;
 };
 
 // cams/%08d_cam.txt.  width / height are not in the file (the reference leaves them

@@ -161,7 +161,7 @@ def hyp_evals_per_view(scan_sizes, runs_per_level=4):
 
 def run_ours(args):
     import torch
-    from acmmp_b200 import host, sharding
+    from acmmp_b200 import host
     rank, local, world, dist = dist_setup(args)
     dev = torch.device("cuda", local)
     sc = make_scan_inputs(args, dev)
@@ -197,6 +197,15 @@ def run_ours(args):
                 torch.empty((H, W), dtype=torch.float32).pin_memory().numpy()) for v in owned}
     n_exchanges = [0]
 
+    # multi-GPU data plane = the library's own NCCL calls on the scan's stream (acmmp_scan_all_gather: no host sync, no
+    # staging copy); torch.distributed only carries the 128-byte NCCL unique id, the barrier and the max over ranks
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(host.nccl_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, src=0)
+        scan.comm_init(bytes(uid.cpu().numpy().tobytes()))
+
     def exchange(ptr, stride, slots):
         if photo_only:          # no stage reads another view's depth map in the photometric-only schedule
             return
@@ -205,11 +214,7 @@ def run_ours(args):
     def gather(ptr, stride, slots):
         if world == 1:
             return
-        seg = int(stride) * int(slots)
-        scan.sync()
-        t = torch.as_tensor(DevPtr(ptr, seg * world), device=dev)
-        sharding.all_gather_segments(t, rank, world, dist)
-        torch.cuda.current_stream().synchronize()
+        scan.all_gather()
         n_exchanges[0] += 1
 
     # kernel time per pyramid level (CUDA events on the launching stream, collected after each level;
@@ -258,11 +263,13 @@ def run_ours(args):
         step(False)
     barrier()
     scan.timing()                      # clear the kernel-time log
+    scan.host_stats()
     l0 = scan.timing()["launches"]
     level_tm.clear()
     with ClockSampler(local) as clocks:
         ms_dev = timed(args.steps, False)
     launches = scan.timing()["launches"] - l0
+    hs = scan.host_stats()              # host side of the planar prior in the timed region: triangulation time, and how long the stream waited for it
     level_tm_timed = {lv: dict(t) for lv, t in level_tm.items()}
     tm = {k: sum(t[k] for t in level_tm_timed.values()) for k in ("init_ms", "sweeps_ms", "tail_ms", "total_ms")}
     step(True)                          # e2e warm-up (pinned staging paths)
@@ -330,7 +337,8 @@ def run_ours(args):
         "config": {"workload": CONFIGS[args.config]["name"].format(W=args.width, H=args.height, n=n, ns=args.nsrc, nl=len(sizes)),
                    "name": args.config,
                    "geom1_order": "in place (the reference's Gauss-Seidel order)" if world == 1 else "Jacobi (sharded scan)",
-                   "levels": [list(s) for s in sizes], "sharding": f"view % {world}", "exchange": "none (no stage reads another view's maps)" if photo_only else "nccl all_gather of depth maps per stage",
+                   "levels": [list(s) for s in sizes], "sharding": f"view % {world}", "exchange": "none (no stage reads another view's maps)" if photo_only else "ncclAllGather of the depth maps per stage, issued by the library on the scan's stream",
+                   "nccl_version": host.nccl_version(),
                    "texels": [p["texels"] for p in per_level],
                    "l2": "inputs (%d images of %.1f MB + per-view state) exceed the 126 MB L2; no explicit flush" % (n, args.width * args.height * 4 / 1e6),
                    "hyp_evals_per_view": hpv},
@@ -366,6 +374,9 @@ def run_ours(args):
                              "ncu --set full capture in profiles/ (1600x1200 level)"},
         "clocks": clocks.summary(),
         "exchanges_per_step": exchanges_per_step,
+        "planar_prior_host": {"delaunay_ms_per_step": hs["prior_host_ms"] / args.steps, "stream_wait_ms_per_step": hs["wait_ms"] / args.steps,
+                              "note": "host triangulation of this rank's views (worker threads, overlapped with device work of the next views); "
+                                      "stream_wait = time the issuing thread was blocked on a triangulation"},
     }
     # bit-level checksum of the final maps of every view (depth from this rank's exchange buffer, i.e.
     # through the NCCL gathers; normals and costs of the owned views summed over ranks): equal numbers
@@ -398,21 +409,30 @@ def run_ours(args):
     # are sent to rank 0 (depths are there already, in the exchange buffer) and rank 0 fuses
     # ("replicas only" for this step).
     gathered = {}
-    if world > 1:
+    if world > 1:                                   # owner -> rank 0 through the library (ncclSend / ncclRecv on the scan's stream)
         for v in range(n):
             w_, h_ = scan.view_size(v)
-            if v % world == rank and rank != 0:
-                _, n_, _ = scan.view_device(v)
-                dist.send(torch.as_tensor(DevPtr(n_, 3 * w_ * h_), device=dev), dst=0)
-            elif rank == 0 and v % world != 0:
-                gathered[v] = torch.empty(3 * w_ * h_, dtype=torch.float32, device=dev)
-                dist.recv(gathered[v], src=v % world)
-        torch.cuda.synchronize()
+            if rank == 0 and v % world != 0:
+                gathered[v] = (torch.empty(3 * w_ * h_, dtype=torch.float32, device=dev), torch.empty(w_ * h_, dtype=torch.float32, device=dev))
+                scan.collect_view(v, 0, gathered[v][0].data_ptr(), gathered[v][1].data_ptr())
+            elif v % world == rank and rank != 0:
+                scan.collect_view(v, 0)
+        scan.sync()
     if rank == 0:
-        fus = host.Fusion(sc["cams"], sc["pairs"], device=local)
+        fcams = []
+        for v in range(n):                      # RescaleImageAndCamera (ACMMP.cpp:179-203): cameras at the size of the maps
+            c = sc["cams"][v].copy()
+            w_, h_ = scan.view_size(v)
+            if (w_, h_) != (c.width, c.height):
+                sx, sy = np.float32(w_) / np.float32(c.width), np.float32(h_) / np.float32(c.height)
+                c.K[0] = float(np.float32(c.K[0]) * sx); c.K[2] = float(np.float32(c.K[2]) * sx)
+                c.K[4] = float(np.float32(c.K[4]) * sy); c.K[5] = float(np.float32(c.K[5]) * sy)
+                c.width, c.height = w_, h_
+            fcams.append(c)
+        fus = host.Fusion(fcams, sc["pairs"], device=local)
         for v in range(n):
             if v in gathered:
-                fus.set_view(v, scan.exchange_view_ptr(v), gathered[v].data_ptr(), on_device=True)
+                fus.set_view(v, scan.exchange_view_ptr(v), gathered[v][0].data_ptr(), on_device=True)
             else:
                 d_, n_, _ = scan.view_device(v)
                 fus.set_view(v, d_, n_, on_device=True)

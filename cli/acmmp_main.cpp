@@ -14,20 +14,54 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <memory>
+#include <thread>
 #include <string>
 #include <vector>
 
 #include "fuse_common.hpp"
+#include "../acmmp_b200/host/driver.hpp"
 
 using namespace acmmp_b200;
 using namespace acmmp_cli;
 
+// --reference_flow: main() of the reference as it stands (main_ACMMP.cpp:89-176) - one ProcessProblem per view and stage,
+// .dmb files between stages, JointBilateralUpsampling between scales - through `class ACMMP` (host/acmmp.hpp, host/driver.hpp).
+// The default mode runs the same schedule resident on the device (class Scan).
+static int reference_flow(const std::string &dense_folder, const std::string &output_folder, std::vector<Problem> &problems, uint64_t seed, int device) {
+    const size_t num_images = problems.size();
+    int max_num_downscale = ComputeMultiScaleSettings(dense_folder, problems, device);
+    bool first_scale = true;
+    uint64_t run = 0;
+    while (max_num_downscale >= 0) {
+        printf("Scale: %d\n", max_num_downscale);
+        for (size_t i = 0; i < num_images; ++i)
+            if (problems[i].num_downscale >= 0) {
+                problems[i].cur_image_size = problems[i].max_image_size / pow(2, problems[i].num_downscale);
+                problems[i].num_downscale--;
+            }
+        bool hierarchy = false;
+        if (!first_scale) {
+            for (size_t i = 0; i < num_images; ++i) JointBilateralUpsampling(dense_folder, output_folder, problems[i], problems[i].cur_image_size, device);
+            hierarchy = true;
+        }
+        first_scale = false;
+        for (size_t i = 0; i < num_images; ++i)
+            ProcessProblem(output_folder, dense_folder, problems, (int)i, false, true, hierarchy, false, seed * 1000003ull + 2 * (run++), true, device);
+        for (int geom_iter = 0; geom_iter < 2; ++geom_iter)
+            for (size_t i = 0; i < num_images; ++i)
+                ProcessProblem(output_folder, dense_folder, problems, (int)i, true, false, false, geom_iter != 0, seed * 1000003ull + 2 * (run++), true, device);
+        max_num_downscale--;
+    }
+    return 0;
+}
+
 int main(int argc, char **argv) {
     std::string dense_folder, output_dir = "/ACMMP", mask_dir = " ", image_dir = "/images";
     float consistency_scalar = 0.3f;
-    int num_consistent_thresh = 1, single_match_penalty = 0, device = 0;
+    int num_consistent_thresh = 1, single_match_penalty = 0, device = 0, gpus = 1;
     unsigned long long seed = 0;
-    bool fuse = true, force_fusion = false, multi_fusion = false, prior = false;
+    bool fuse = true, force_fusion = false, multi_fusion = false, prior = false, ref_flow = false;
     std::string fusion_dir = "/ACMMP";
     bool renamed_outdir = false;
     for (int i = 1; i < argc; ++i) {
@@ -41,7 +75,7 @@ int main(int argc, char **argv) {
         };
         if (a == "-h" || a == "--help") {
             printf("usage: acmmp_main <dense_folder> [--output_dir /ACMMP] [-f|--fuse_thresh 0.3] [--num_consistent_thresh 1]\n"
-                   "                  [--mask_dir DIR] [--image_override DIR] [--device 0] [--seed N] [--no_fusion]\n"
+                   "                  [--mask_dir DIR] [--image_override DIR] [--device 0] [--gpus N] [--seed N] [--no_fusion] [--reference_flow]\n"
                    "                  [--force_fusion] [--multi_fusion [/DIR]] [--single_match_penalty N] [-p|--prior]\n");
             return 1;
         } else if (a == "--dense_folder") dense_folder = value("--dense_folder");
@@ -54,8 +88,10 @@ int main(int argc, char **argv) {
         else if (a == "--mask_dir") mask_dir = value("--mask_dir");
         else if (a == "--image_override") image_dir = value("--image_override");
         else if (a == "--device") device = atoi(value("--device"));
+        else if (a == "--gpus") gpus = atoi(value("--gpus"));
         else if (a == "--seed") seed = strtoull(value("--seed"), nullptr, 10);
         else if (a == "--no_fusion") fuse = false;
+        else if (a == "--reference_flow") ref_flow = true;
         else if (a == "--force_fusion") force_fusion = true;
         else if (a == "--multi_fusion") {   // implicit value "/ACMMP" (main_ACMMP.cpp:31)
             multi_fusion = true;
@@ -70,6 +106,10 @@ int main(int argc, char **argv) {
     }
     if (dense_folder.empty()) {
         fprintf(stderr, "no dense_folder given\n");
+        return EXIT_FAILURE;
+    }
+    if (gpus < 1) {
+        fprintf(stderr, "--gpus must be >= 1\n");
         return EXIT_FAILURE;
     }
     try {
@@ -112,8 +152,50 @@ int main(int argc, char **argv) {
         const std::string output_folder = dense_folder + output_dir;
         mkdir(output_folder.c_str(), 0777);
 
-        Scan scan(cams, pairs, device);
-        for (int i = 0; i < n; ++i) scan.SetImageU8(i, ToGray8(images[i]));
+        if (ref_flow) {
+            if (prior || force_fusion || multi_fusion) {
+                fprintf(stderr, "--reference_flow runs the plain schedule (no -p / --force_fusion / --multi_fusion)\n");
+                return EXIT_FAILURE;
+            }
+            reference_flow(dense_folder, output_folder, problems, seed, device);
+            printf("depth maps written to %s\n", output_folder.c_str());
+            if (fuse) {
+                std::vector<acmmp_camera> cams_out(n);
+                std::vector<Map<float>> depths(n), normals(n);
+                for (int i = 0; i < n; ++i) {
+                    const std::string folder = ACMMP::ResultFolder(output_folder, problems[i].ref_image_id);
+                    if (readDepthDmb(folder + "/depths_geom.dmb", depths[i]) || readNormalDmb(folder + "/normals.dmb", normals[i])) {
+                        fprintf(stderr, "cannot read the maps under %s\n", folder.c_str());
+                        return EXIT_FAILURE;
+                    }
+                    cams_out[i] = CameraAtMapSize(cams[i], depths[i].cols, depths[i].rows);
+                }
+                FuseOptions o;
+                o.dense_folder = dense_folder;
+                o.output_folder = output_folder;
+                o.image_dir = image_dir;
+                o.mask_dir = mask_dir;
+                o.consistency_scalar = consistency_scalar;
+                o.num_consistent_thresh = num_consistent_thresh;
+                o.device = device;
+                if (FuseAndStore(o, problems, cams_out, pairs, [&](int i, Map<float> &d, Map<float> &nrm) {
+                        d = depths[i];
+                        nrm = normals[i];
+                        return true;
+                    }) < 0)
+                    return EXIT_FAILURE;
+            }
+            return 0;
+        }
+        // --gpus N: the views are sharded over N devices (view v belongs to rank v % N), one host thread and one resident
+        // scan per device; after every stage the depth maps are all-gathered by the library (ncclAllGather on the scans'
+        // streams, communicators from ncclCommInitAll).  N = 1 is the same code without a communicator.
+        std::vector<std::unique_ptr<Scan>> scans;
+        for (int r = 0; r < gpus; ++r) {
+            scans.emplace_back(new Scan(cams, pairs, gpus > 1 ? r : device, r, gpus));
+            for (int i = 0; i < n; ++i) scans[r]->SetImageU8(i, ToGray8(images[i]));
+        }
+        if (gpus > 1) Scan::CommInitAll(scans);
         if (prior) {
             // the reference numbers the prior images by problem index, not by image id (acmmp_definitions.cpp:278, :104-105)
             for (int i = 0; i < n; ++i) {
@@ -124,28 +206,48 @@ int main(int argc, char **argv) {
                     fprintf(stderr, "Initialisation from a prior was requested, but no suitable priors were found: %s\n", err.c_str());
                     return -1;
                 }
-                scan.SetPriorMaps(i, d16, n16);
+                for (auto &sc : scans) sc->SetPriorMaps(i, d16, n16);
             }
         }
         std::vector<Map<float>> photo_depth(n);
-        const int levels = scan.NumLevels();
-        for (int level = 0; level < levels; ++level) {
-            printf("Scale: %d\n", levels - 1 - level);
-            scan.BeginLevel(level);
-            for (int stage = ACMMP_STAGE_PHOTO; stage <= ACMMP_STAGE_GEOM1; ++stage) {
-                scan.RunStage(stage, seed);
-                if (level == levels - 1 && stage == ACMMP_STAGE_PHOTO)   // depths.dmb = the photometric + planar-prior result
-                    for (int i = 0; i < n; ++i) scan.GetView(i, &photo_depth[i], nullptr, nullptr);
+        const int levels = scans[0]->NumLevels();
+        std::vector<std::string> errors(gpus);
+        auto drive = [&](int r) {
+            try {
+                Scan &scan = *scans[r];
+                for (int level = 0; level < levels; ++level) {
+                    if (r == 0) printf("Scale: %d\n", levels - 1 - level);
+                    scan.BeginLevel(level);
+                    for (int stage = ACMMP_STAGE_PHOTO; stage <= ACMMP_STAGE_GEOM1; ++stage) {
+                        scan.RunStage(stage, seed);
+                        scan.AllGather();
+                        if (r == 0 && level == levels - 1 && stage == ACMMP_STAGE_PHOTO)   // depths.dmb = the photometric + planar-prior result
+                            for (int i = 0; i < n; ++i) scan.GetView(i, &photo_depth[i], nullptr, nullptr);
+                    }
+                }
+                scan.Sync();
+            } catch (const std::exception &e) {
+                errors[r] = e.what();
             }
+        };
+        if (gpus == 1) {
+            drive(0);
+        } else {
+            std::vector<std::thread> threads;
+            for (int r = 0; r < gpus; ++r) threads.emplace_back(drive, r);
+            for (auto &t : threads) t.join();
         }
-        scan.Sync();
+        for (int r = 0; r < gpus; ++r)
+            if (!errors[r].empty()) throw std::runtime_error("rank " + std::to_string(r) + ": " + errors[r]);
+        // every rank holds every depth map (exchange buffer); normals and costs live on the owner
+        auto get_view = [&](int i, Map<float> *d, Map<float> *nrm, Map<float> *c) { scans[i % gpus]->GetView(i, d, nrm, c); };
         // acmmp_definitions.cpp:392-401: one folder per reference image
         std::vector<acmmp_camera> cams_out(n);
         for (int i = 0; i < n; ++i) {
             const std::string folder = output_folder + "/2333_" + id_name(problems[i].ref_image_id, "");
             mkdir(folder.c_str(), 0777);
             Map<float> depth, normal, cost;
-            scan.GetView(i, &depth, &normal, &cost);
+            get_view(i, &depth, &normal, &cost);
             if (writeDepthDmb(folder + "/depths.dmb", photo_depth[i]) || writeDepthDmb(folder + "/depths_geom.dmb", depth) ||
                 writeNormalDmb(folder + "/normals.dmb", normal) || writeDepthDmb(folder + "/costs.dmb", cost)) {
                 fprintf(stderr, "cannot write maps under %s\n", folder.c_str());
@@ -168,7 +270,7 @@ int main(int argc, char **argv) {
             o.device = device;
             // colour and mask come from the host, so the maps take the same way (one flag per call)
             if (FuseAndStore(o, problems, cams_out, pairs, [&](int i, Map<float> &d, Map<float> &nrm) {
-                    scan.GetView(i, &d, &nrm, nullptr);
+                    get_view(i, &d, &nrm, nullptr);
                     return true;
                 }) < 0)
                 return EXIT_FAILURE;

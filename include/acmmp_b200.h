@@ -368,6 +368,28 @@ int acmmp_scan_level_is_u8(const acmmp_scan *s);
  * meaningful with world == 1.  0 = Jacobi (geom-1 reads the geom-0 maps of all
  * views).  -1 = default: 1 on an unsharded scan, 0 on a sharded one. */
 int acmmp_scan_set_sequential_geom(acmmp_scan *s, int on);
+
+/* ---- multi-GPU: NCCL inside the library ----------------------------------------------
+ * The reference is single-GPU (acmmp_definitions.cpp:253).  A sharded scan (acmmp_scan_set_shard) exchanges the
+ * depth maps of the owned views after every stage - the only data that crosses views (ACMMP.cpp:608-635) - with ONE
+ * ncclAllGather on the scan's own stream: no host synchronisation, no staging copy.  libnccl.so.2 is loaded with
+ * dlopen() on first use (the copy a torch process already holds, else the system's); acmmp_nccl_version() is 0 when
+ * it is missing.
+ *   one process per GPU:  rank 0 calls acmmp_nccl_get_unique_id and hands the 128 bytes to the other ranks by any
+ *                         means (torch.distributed broadcast, MPI, a file); every rank then calls acmmp_scan_comm_init.
+ *   one thread per GPU:   acmmp_scan_comm_init_all(scans, n) (ncclCommInitAll); each thread drives its own scan.
+ * acmmp_scan_all_gather: call after every acmmp_scan_run_stage (a no-op on an unsharded scan).
+ * acmmp_scan_collect_view: owner -> `root`, normals (3 f32 / px) + costs of one view into device buffers the root
+ * provides (ncclSend / ncclRecv; every rank may call it, only owner and root act): brings the final maps to the rank
+ * that fuses. */
+#define ACMMP_NCCL_ID_BYTES 128
+int acmmp_nccl_version(void);
+int acmmp_nccl_get_unique_id(uint8_t id[ACMMP_NCCL_ID_BYTES]);
+int acmmp_scan_comm_init(acmmp_scan *s, const uint8_t id[ACMMP_NCCL_ID_BYTES]);
+int acmmp_scan_comm_init_all(acmmp_scan *const *scans, int n);
+int acmmp_scan_comm_destroy(acmmp_scan *s);
+int acmmp_scan_all_gather(acmmp_scan *s);
+int acmmp_scan_collect_view(acmmp_scan *s, int view, int root, float *d_normal3, float *d_cost);
 /* Reduced schedules (before the first level).  single_scale: every view at its (capped) full size from the
  * start, no pyramid (ComputeMultiScaleSettings, acmmp_definitions.cpp:207-243, switched off).
  * photometric_only: the photometric stage is ONE RunPatchMatch per view, without the planar-prior construction

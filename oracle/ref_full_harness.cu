@@ -154,6 +154,7 @@ extern "C" int ref_full_run(const char *dense_folder_c, const char *output_dir_c
     }
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
+    (void)cudaGetLastError();   // ~ACMMP frees members it never allocated (ACMMP.cpp:109-151): not the caller's error
     return 0;
 }
 
@@ -237,6 +238,8 @@ extern "C" int ref_full_capture_prior(const char *dense_folder_c, const char *ou
     g_capture = true;
     ProcessProblem(sample_handler, output_folder, dense_folder, problems, idx, false, true, false, false, false);
     g_capture = false;
+    cudaDeviceSynchronize();
+    (void)cudaGetLastError();   // see ref_full_run
     if (g_cap_mask.empty() || g_cap_depth.empty()) return -1;
     *w = g_cap_mask.cols;
     *h = g_cap_mask.rows;

@@ -441,3 +441,73 @@ def dropin_run(dense, seed=1234, fuse=True, consistency_scalar=0.3, num_consiste
             os.dup2(saved, 1)
             os.close(saved)
     assert rc == 0
+
+
+# ---- the reference's own planar-prior functions (ACMMP.cpp:868-958) and what its ProcessProblem builds -------------
+def full_support_points(cam, costs):
+    """ACMMP::GetSupportPoints of the reference on a cost map (host code; no GPU needed)"""
+    lib = _full_lib()
+    c = np.ascontiguousarray(costs, np.float32)
+    h, w = c.shape
+    cc = cam.copy()
+    cc.width, cc.height = w, h
+    cap = ((w + 4) // 5) * ((h + 4) // 5)
+    xy = np.zeros((cap, 2), np.int32)
+    lib.ref_full_support_points.argtypes = [C.POINTER(L.Camera), C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_int]
+    n = lib.ref_full_support_points(C.byref(cc), L.fptr(c), xy.ctypes.data_as(C.POINTER(C.c_int)), cap)
+    return xy[:n]
+
+
+def full_prior_planes(cam, depth, tris):
+    """ACMMP::GetPriorPlaneParams of the reference for every triangle (cv::SVD::solveZ: the stand-in's cross product)"""
+    lib = _full_lib()
+    d = np.ascontiguousarray(depth, np.float32)
+    cc = cam.copy()
+    cc.height, cc.width = d.shape
+    t = np.ascontiguousarray(tris, np.int32).reshape(-1, 6)
+    out = np.zeros((len(t), 4), np.float32)
+    lib.ref_full_prior_planes.argtypes = [C.POINTER(L.Camera), C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_float)]
+    lib.ref_full_prior_planes(C.byref(cc), L.fptr(d), t.ctypes.data_as(C.POINTER(C.c_int)), len(t), L.fptr(out))
+    return out
+
+
+def full_depths_from_planes(cam, planes, xy):
+    """ACMMP::GetDepthFromPlaneParam of the reference at pixels xy (n, 2) for planes (n, 4)"""
+    lib = _full_lib()
+    p = np.ascontiguousarray(planes, np.float32).reshape(-1, 4)
+    q = np.ascontiguousarray(xy, np.int32).reshape(-1, 2)
+    out = np.zeros(len(p), np.float32)
+    cc = cam.copy()
+    lib.ref_full_depths_from_planes.argtypes = [C.POINTER(L.Camera), C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_float)]
+    lib.ref_full_depths_from_planes(C.byref(cc), L.fptr(p), q.ctypes.data_as(C.POINTER(C.c_int)), len(p), L.fptr(out))
+    return out
+
+
+def full_capture_prior(dense, idx=0, seed=1234, output_dir="/ACMMP_CAPTURE"):
+    """One ProcessProblem (photometric + planar prior) of the reference program on view `idx`; returns what its driver built:
+    dict(depth (h, w) the prior was built from, points (n, 2), tris (m, 6), planes (k, 4) = planeParams_tri,
+    mask (h, w) float = mask_tri after the range check).  Needs a GPU (RunPatchMatch)."""
+    lib = _full_lib()
+    ip = C.POINTER(C.c_int)
+    lib.ref_full_capture_prior.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_uint64, ip, ip, ip, ip, ip]
+    lib.ref_full_captured.argtypes = [C.POINTER(C.c_float), ip, ip, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    w, h, ns, nt, npl = C.c_int(), C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    import sys
+    sys.stdout.flush()
+    saved = os.dup(1)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    os.dup2(devnull, 1)
+    os.close(devnull)
+    try:
+        rc = lib.ref_full_capture_prior(dense.encode(), output_dir.encode(), idx, seed, C.byref(w), C.byref(h), C.byref(ns), C.byref(nt), C.byref(npl))
+    finally:
+        os.dup2(saved, 1)
+        os.close(saved)
+    assert rc == 0
+    depth = np.zeros((h.value, w.value), np.float32)
+    mask = np.zeros((h.value, w.value), np.float32)
+    pts = np.zeros((ns.value, 2), np.int32)
+    tris = np.zeros((nt.value, 6), np.int32)
+    planes = np.zeros((npl.value, 4), np.float32)
+    assert lib.ref_full_captured(L.fptr(depth), pts.ctypes.data_as(ip), tris.ctypes.data_as(ip), L.fptr(planes), L.fptr(mask)) == 0
+    return {"depth": depth, "points": pts, "tris": tris, "planes": planes, "mask": mask}

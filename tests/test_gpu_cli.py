@@ -285,3 +285,30 @@ def test_fuse_data_refuses_the_output_folder_like_the_reference(cli_run):
     out = subprocess.run([exe, dense], capture_output=True, text=True)
     os.rename(os.path.join(outdir, "2333_%08d" % ids[1], "normals.bak"), os.path.join(outdir, "2333_%08d" % ids[1], "normals.dmb"))
     assert out.returncode != 0 and "cannot read the maps" in out.stderr
+
+
+def test_cli_reference_flow_through_the_cpp_class(cli_run):
+    """--reference_flow: the reference's own flow - ProcessProblem per view and stage with .dmb hand-over, host planar
+    prior, JBU between scales - written against `class ACMMP` with the reference's method signatures
+    (acmmp_b200/host/acmmp.hpp, driver.hpp).  Same scene as the resident run: the two flows must agree like two seeds."""
+    sc, dense, ids, _ = cli_run
+    n = len(ids)
+    out = subprocess.run([EXE, dense, "--seed", "5", "--output_dir", "/FLOW", "--reference_flow"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    assert out.stdout.count("Run Planar Prior Assisted PatchMatch MVS") == n and out.stdout.count("Processing image") == 2 * 3 * n
+    inner = (slice(8, -8), slice(8, -8))
+    for i in range(n):
+        flow = read_dmb(os.path.join(dense, "FLOW", "2333_%08d" % ids[i], "depths_geom.dmb"))
+        resident = read_dmb(os.path.join(dense, "ACMMP", "2333_%08d" % ids[i], "depths_geom.dmb"))
+        gt = sc["depths"][i]
+        acc_flow = (np.abs(flow - gt)[inner] / gt[inner] < 0.01).mean()
+        acc_res = (np.abs(resident - gt)[inner] / gt[inner] < 0.01).mean()
+        assert acc_flow >= 0.9 and abs(acc_flow - acc_res) <= 0.01, (acc_flow, acc_res)
+        assert (np.abs(flow - resident)[inner] / gt[inner] < 0.001).mean() >= 0.93
+        for name in ("depths.dmb", "normals.dmb", "costs.dmb"):
+            assert os.path.exists(os.path.join(dense, "FLOW", "2333_%08d" % ids[i], name))
+    xyz_flow, _ = read_ply(os.path.join(dense, "FLOW", "ACMMP_model.ply"))
+    xyz_res, _ = read_ply(os.path.join(dense, "ACMMP", "ours.ply")) if os.path.exists(os.path.join(dense, "ACMMP", "ours.ply")) else (None, None)
+    assert len(xyz_flow) > 50000
+    if xyz_res is not None:
+        assert abs(len(xyz_flow) - len(xyz_res)) <= 0.01 * len(xyz_res), (len(xyz_flow), len(xyz_res))
