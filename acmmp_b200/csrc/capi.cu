@@ -13,6 +13,7 @@
 #include <chrono>
 #include <cstring>
 #include <string>
+#include <array>
 #include <vector>
 
 #include "../../include/acmmp_b200.h"
@@ -84,6 +85,8 @@ struct acmmp_ctx {
     // event quads (start, after init, after sweeps, after tail) of every acmmp_run since the
     // last acmmp_timing_collect; the newest quad also serves acmmp_last_timing
     std::vector<cudaEvent_t> evpool;
+    std::vector<int> quad_tag;   // run_tag of every quad (the scan tags runs with their pyramid level)
+    int run_tag = 0;
     size_t ev_used = 0;
     size_t last_quad = 0;
     bool have_quad = false;
@@ -659,3 +662,4 @@ int acmmp_set_planar_prior(acmmp_ctx *ctx, const float *planes4, const uint32_t 
 #include "capi_run.cu.inc"
 #include "capi_scan.cu.inc"
 #include "capi_nccl.cu.inc"
+#include "capi_dataflow.cu.inc"

@@ -312,6 +312,24 @@ def measure_tex_peak(device=0, u8=False):
 STAGE_PHOTO, STAGE_GEOM0, STAGE_GEOM1 = 0, 1, 2
 
 
+def plan_dataflow(pairs, n_levels, world, photometric_only=False):
+    """host only: (task_round, task_rank, n_rounds, lag) of the dataflow schedule; task = stage * n_views + view"""
+    lib = L.load()
+    n = len(pairs)
+    off = np.zeros(n + 1, np.int32)
+    off[1:] = np.cumsum([len(p) for p in pairs])
+    ids = np.asarray([i for p in pairs for i in p], np.int32)
+    T = n_levels * (1 if photometric_only else 3) * n
+    rounds, ranks = np.zeros(T, np.int32), np.zeros(T, np.int32)
+    nr, lag = C.c_int32(0), C.c_int32(0)
+    I32 = C.POINTER(C.c_int32)
+    rc = lib.acmmp_plan_dataflow(n, off.ctypes.data_as(I32), ids.ctypes.data_as(I32), n_levels, int(photometric_only), world,
+                                 rounds.ctypes.data_as(I32), ranks.ctypes.data_as(I32), C.byref(nr), C.byref(lag))
+    if rc:
+        raise RuntimeError("acmmp_plan_dataflow failed (%d)" % rc)
+    return rounds, ranks, nr.value, lag.value
+
+
 def nccl_version():
     return int(L.load().acmmp_nccl_version())
 
@@ -402,9 +420,43 @@ class Scan:
         buf = (C.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
         self._ck(self._lib.acmmp_scan_comm_init(self._s, buf), "comm_init")
 
+    @staticmethod
+    def comm_init_all(scans):
+        """one process, one scan (and one thread) per GPU: scans[r] = rank r of len(scans) on distinct devices (ncclCommInitAll)"""
+        arr = (C.c_void_p * len(scans))(*[s._s for s in scans])
+        rc = scans[0]._lib.acmmp_scan_comm_init_all(arr, len(scans))
+        if rc != 0:
+            raise L.AcmmpError(f"comm_init_all failed ({rc}): {scans[0]._lib.acmmp_scan_last_error(scans[0]._s).decode()}")
+
     def all_gather(self):
         """depth maps of the owned views -> every rank, on the scan's stream (no host sync); no-op when unsharded"""
         self._ck(self._lib.acmmp_scan_all_gather(self._s), "all_gather")
+
+    def run_dataflow(self, seed):
+        """the whole scan (all levels, all stages) as a dataflow of (stage, view) tasks; collective on a sharded scan.
+        Afterwards every rank holds every view's final maps (get_view / view_device)."""
+        self._ck(self._lib.acmmp_scan_run_dataflow(self._s, C.c_uint64(seed)), "run_dataflow")
+
+    def keep_photometric(self, on=True):
+        self._ck(self._lib.acmmp_scan_keep_photometric(self._s, int(bool(on))), "keep_photometric")
+
+    def photometric_depth(self, view):
+        """depths.dmb of the reference: the finest level's photometric (+ prior) depth, kept by keep_photometric()"""
+        w, h = self.view_size(view)
+        out = np.empty((h, w), np.float32)
+        self._ck(self._lib.acmmp_scan_get_photometric_depth(self._s, view, out.ctypes.data_as(C.c_void_p)), "photometric_depth")
+        return out
+
+    def level_stats(self, level):
+        """kernel time by phase (+ NCC counts of a counted dataflow run, texel format) of one pyramid level since the last call"""
+        ms, ncc, u8 = (C.c_double * 4)(), (C.c_uint64 * 2)(), C.c_int(0)
+        self._ck(self._lib.acmmp_scan_level_stats(self._s, level, ms, ncc, C.byref(u8)), "level_stats")
+        return {"init_ms": ms[0], "sweeps_ms": ms[1], "tail_ms": ms[2], "total_ms": ms[3], "init": int(ncc[0]), "sweeps": int(ncc[1]), "u8": bool(u8.value)}
+
+    def dataflow_stats(self):
+        r, lag = C.c_int(0), C.c_int(0)
+        self._ck(self._lib.acmmp_scan_dataflow_stats(self._s, C.byref(r), C.byref(lag)), "dataflow_stats")
+        return {"rounds": r.value, "lag": lag.value}
 
     def collect_view(self, view, root, d_normal3=None, d_cost=None):
         """owner -> root: normals + costs of `view` into the root's device buffers (int pointers)"""

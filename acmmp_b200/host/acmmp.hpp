@@ -355,6 +355,16 @@ public:
     void Sync() { check(acmmp_scan_sync(s_)); }
     // sharded scans: the depth maps of the owned views -> every rank (ncclAllGather on the scan's stream; no-op when unsharded)
     void AllGather() { check(acmmp_scan_all_gather(s_)); }
+    // the whole scan as a dataflow of (stage, view) tasks (all levels, all stages; collective on a sharded scan);
+    // afterwards every rank serves every view's final maps
+    void RunDataflow(uint64_t seed) { check(acmmp_scan_run_dataflow(s_, seed)); }
+    void KeepPhotometric(bool on) { check(acmmp_scan_keep_photometric(s_, on ? 1 : 0)); }
+    void GetPhotometricDepth(int view, Map<float> &depth) {
+        int w = 0, h = 0;
+        ViewSize(view, w, h);
+        depth = Map<float>(h, w, 1);
+        check(acmmp_scan_get_photometric_depth(s_, view, depth.data.data()));
+    }
     // one process, one scan per GPU: communicators for scans[r] = rank r of scans.size() (ncclCommInitAll)
     template <class Ptr> static void CommInitAll(const std::vector<Ptr> &scans) {
         std::vector<acmmp_scan *> handles;

@@ -67,6 +67,7 @@ def parse_args():
     ap.add_argument("--nsrc", type=int, default=None)
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--staged", action="store_true", help="N > 1: the stage-by-stage loop (view %% N, all-gather after every stage) instead of the dataflow schedule")
     ap.add_argument("--tex-format", default="auto", choices=["auto", "r32f"],
                     help="auto: R8 unorm texels on levels that are not resized (bit-identical samples); r32f: float texels everywhere")
     ap.add_argument("--ref-views", type=int, default=4, help="views of the reference arm's kernel-only pass (bounded sample)")
@@ -184,6 +185,19 @@ def run_ours(args):
     stages = (host.STAGE_PHOTO,) if photo_only else (host.STAGE_PHOTO, host.STAGE_GEOM0, host.STAGE_GEOM1)
     runs_per_level = 1 if photo_only else 4            # RunPatchMatch per view per level
     owned = scan.owned()
+    # N > 1: the whole scan as a dataflow of (stage, view) tasks (acmmp_scan_run_dataflow) - no stage barrier
+    dataflow = world > 1 and not args.staged
+    n_levels = scan.num_levels()
+    if dataflow:
+        _, task_rank, n_rounds, df_lag = host.plan_dataflow(sc["pairs"], n_levels, world, photo_only)
+        per = 1 if photo_only else 3
+        runs_rank = [0] * n_levels               # RunPatchMatch calls of this rank per level
+        for t, r in enumerate(task_rank.tolist()):
+            g = t // n
+            if r == rank:
+                runs_rank[g // per] += (1 if photo_only else 2) if g % per == 0 else 1
+    else:
+        runs_rank = [(1 if photo_only else 4) * len(owned)] * n_levels
     # size of the maps a step hands back = the finest level (the 3200 cap of ACMMP.h:36 applies to eth3d)
     cap = 3200
     fmax = max(args.width, args.height)
@@ -236,7 +250,10 @@ def run_ours(args):
                 scan.set_image_u8(v, imgs_np[v], sync=False)
             else:
                 scan.set_image(v, imgs_dev[v].data_ptr(), on_device=True)
-        scan.run_all(seed=1234, exchange=exchange, level_done=level_done, stages=stages)
+        if dataflow:
+            scan.run_dataflow(1234)
+        else:
+            scan.run_all(seed=1234, exchange=exchange, level_done=level_done, stages=stages)
         if e2e:
             for v in owned:
                 scan.get_view(v, out=outs[v])
@@ -268,6 +285,11 @@ def run_ours(args):
     level_tm.clear()
     with ClockSampler(local) as clocks:
         ms_dev = timed(args.steps, False)
+    if dataflow:
+        for lv in range(n_levels):
+            t = scan.level_stats(lv)
+            level_tm[lv] = {k: t[k] for k in ("init_ms", "sweeps_ms", "tail_ms", "total_ms")}
+            level_u8[lv] = t["u8"]
     launches = scan.timing()["launches"] - l0
     hs = scan.host_stats()              # host side of the planar prior in the timed region: triangulation time, and how long the stream waited for it
     level_tm_timed = {lv: dict(t) for lv, t in level_tm.items()}
@@ -292,9 +314,17 @@ def run_ours(args):
     scan.reset()
     for v in range(n):
         scan.set_image(v, imgs_dev[v].data_ptr(), on_device=True)
-    scan.run_all(seed=1234, exchange=exchange, level_done=count_level, stages=stages)
-    scan.sync()
-    exchanges_per_step = n_exchanges[0] - ex0
+    if dataflow:
+        scan.run_dataflow(1234)
+        scan.sync()
+        for lv in range(n_levels):
+            t = scan.level_stats(lv)
+            ncc_level[lv] = {"init": t["init"], "sweeps": t["sweeps"]}
+        exchanges_per_step = scan.dataflow_stats()["rounds"]
+    else:
+        scan.run_all(seed=1234, exchange=exchange, level_done=count_level, stages=stages)
+        scan.sync()
+        exchanges_per_step = n_exchanges[0] - ex0
     ncc = {k: sum(c[k] for c in ncc_level.values()) for k in ("init", "sweeps")}
     scan.count_ncc(False)
     fp32_tflops, mufu_gops = host.measure_fp32_peak(local)
@@ -305,7 +335,7 @@ def run_ours(args):
     top_u8 = bool(level_u8.get(top, False))
     top_sweep_s = level_tm_timed[top]["sweeps_ms"] * 1e-3
     top_fetches = ncc_level[top]["sweeps"] * 36 * args.steps
-    top_launches = runs_per_level * 4 * len(owned) * args.steps   # 4 half-sweeps per RunPatchMatch
+    top_launches = runs_rank[top] * 4 * args.steps   # 4 half-sweeps per RunPatchMatch
     top_peak, top_grouped = (tex8_coherent, tex8_grouped) if top_u8 else (tex_coherent, tex_grouped)
     top_achieved = top_fetches / top_sweep_s / 1e9
     per_level = []
@@ -321,12 +351,13 @@ def run_ours(args):
     #  reference formulation: per run P * 28 hypotheses * nsrc views, 1538 flop each
     #  executed: counted NCC evaluations x 36 bilinear fetches (the kernel scores the current plane and
     #  the 5 refinement candidates against the sampled views only)
-    ncc_sweeps = sum(runs_per_level * w * h * 28 * args.nsrc for (w, h) in sizes) * len(owned) * args.steps
+    ncc_sweeps = sum(runs_rank[lv] * w * h * 28 * args.nsrc for lv, (w, h) in enumerate(sizes)) * args.steps
     sweep_s = tm["sweeps_ms"] * 1e-3
     fp32_achieved = ncc_sweeps * FLOP_PER_NCC / sweep_s / 1e12
     fetches = ncc["sweeps"] * 36 * args.steps
     tex_achieved = fetches / sweep_s / 1e9
-    n_sweep_launches = runs_per_level * 4 * len(owned) * len(sizes) * args.steps   # runs x 4 half-sweeps per view per level
+    n_sweep_launches = 4 * sum(runs_rank) * args.steps   # runs x 4 half-sweeps
+    views_rank = sum(runs_rank) / float(runs_per_level * len(sizes))   # this rank's RunPatchMatch calls, in whole-view equivalents
     h2d = sum(int(np.prod(im.shape)) for im in imgs_np)   # uint8
     d2h = len(owned) * H * W * 5 * 4
     line = {
@@ -337,7 +368,13 @@ def run_ours(args):
         "config": {"workload": CONFIGS[args.config]["name"].format(W=args.width, H=args.height, n=n, ns=args.nsrc, nl=len(sizes)),
                    "name": args.config,
                    "geom1_order": "in place (the reference's Gauss-Seidel order)" if world == 1 else "Jacobi (sharded scan)",
-                   "levels": [list(s) for s in sizes], "sharding": f"view % {world}", "exchange": "none (no stage reads another view's maps)" if photo_only else "ncclAllGather of the depth maps per stage, issued by the library on the scan's stream",
+                   "levels": [list(s) for s in sizes],
+                   "schedule": ("dataflow: %d (stage, view) tasks in %d rounds of %d, lag %d (acmmp_scan_run_dataflow)" % (len(task_rank), n_rounds, world, df_lag)) if dataflow
+                               else ("stage by stage, view %% %d" % world),
+                   "sharding": "tasks dealt to ranks round by round" if dataflow else f"view % {world}",
+                   "exchange": ("grouped ncclBroadcast of the records [depth|normal|cost] a round wrote, issued by the library on its second stream, overlapped with the next round" if dataflow
+                                else "none (no stage reads another view's maps)" if photo_only
+                                else "ncclAllGather of the depth maps per stage, issued by the library on the scan's stream"),
                    "nccl_version": host.nccl_version(),
                    "texels": [p["texels"] for p in per_level],
                    "l2": "inputs (%d images of %.1f MB + per-view state) exceed the 126 MB L2; no explicit flush" % (n, args.width * args.height * 4 / 1e6),
@@ -349,8 +386,8 @@ def run_ours(args):
         "kernel_ms_per_step": {k: tm[k] / args.steps for k in ("init_ms", "sweeps_ms", "tail_ms", "total_ms")},
         # the RunPatchMatch kernels alone (CUDA events around init / sweeps / tail of every run, this rank): what the
         # reference arm's `kernel_only` is compared with - the rest of `value` is schedule (prior construction, JBU, copies)
-        "kernel_only": {"value": len(owned) * args.steps / (tm["total_ms"] * 1e-3), "unit": "views/s (this rank's views / its RunPatchMatch kernel time)",
-                        "ms_per_view": tm["total_ms"] / (len(owned) * args.steps)},
+        "kernel_only": {"value": views_rank * args.steps / (tm["total_ms"] * 1e-3), "unit": "views/s (this rank's share of the scan's RunPatchMatch calls, in views / its kernel time)",
+                        "ms_per_view": tm["total_ms"] / (views_rank * args.steps)},
         "roofline": {"bound": "tex", "kernel": "sweep_kernel<%s> at %dx%d" % ("R8" if top_u8 else "R32F", sizes[top][0], sizes[top][1]),
                      "achieved": top_achieved, "peak": top_peak, "unit": "Gfetch/s",
                      "frac": top_achieved / top_peak,
@@ -385,13 +422,16 @@ def run_ours(args):
     # which a sharded scan cannot follow)
     scan.set_sequential_geom(False)
     scan.reset()
-    scan.run_all(seed=1234, exchange=exchange, stages=stages)
-    if photo_only:
-        gather(*scan.exchange_info())
+    if dataflow:
+        scan.run_dataflow(1234)
+    else:
+        scan.run_all(seed=1234, exchange=exchange, stages=stages)
+        if photo_only:
+            gather(*scan.exchange_info())
     scan.sync()
     csum = torch.zeros(1, dtype=torch.int64, device=dev)
     for v in range(n):
-        d_, _, _ = scan.view_device(v) if v in owned else (scan.exchange_view_ptr(v), None, None)
+        d_, _, _ = scan.view_device(v) if (v in owned or dataflow) else (scan.exchange_view_ptr(v), None, None)
         w_, h_ = scan.view_size(v)
         csum += torch.as_tensor(DevPtr(d_, w_ * h_), device=dev).view(torch.int32).to(torch.int64).sum() * (v + 1)
     own = torch.zeros(1, dtype=torch.int64, device=dev)
@@ -409,7 +449,7 @@ def run_ours(args):
     # are sent to rank 0 (depths are there already, in the exchange buffer) and rank 0 fuses
     # ("replicas only" for this step).
     gathered = {}
-    if world > 1:                                   # owner -> rank 0 through the library (ncclSend / ncclRecv on the scan's stream)
+    if world > 1 and not dataflow:                  # owner -> rank 0 through the library (ncclSend / ncclRecv on the scan's stream)
         for v in range(n):
             w_, h_ = scan.view_size(v)
             if rank == 0 and v % world != 0:
@@ -443,7 +483,7 @@ def run_ours(args):
         fst = fus.stats()
         line["fusion"] = {"points": int(npts), "ms": fwall * 1e3, "device_ms": fst["score_ms"] + fst["greedy_ms"] + fst["emit_ms"],
                           "fixed_point_rounds_max": max(fst["rounds"]), "consistency_scalar": 0.3, "num_consistent_thresh": 1,
-                          "where": "rank 0" + (" after gathering the normals over NCCL" if world > 1 else "")}
+                          "where": "rank 0" + ((" (holds every view's record after the dataflow run)" if dataflow else " after gathering the normals over NCCL") if world > 1 else "")}
         if world == 1 and not args.no_cpu_baseline and args.config == "full":
             import oraclebind as ob
             maps = [scan.get_view(v, want_cost=False) for v in range(n)]

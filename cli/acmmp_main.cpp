@@ -61,7 +61,7 @@ int main(int argc, char **argv) {
     float consistency_scalar = 0.3f;
     int num_consistent_thresh = 1, single_match_penalty = 0, device = 0, gpus = 1;
     unsigned long long seed = 0;
-    bool fuse = true, force_fusion = false, multi_fusion = false, prior = false, ref_flow = false;
+    bool fuse = true, force_fusion = false, multi_fusion = false, prior = false, ref_flow = false, staged = false;
     std::string fusion_dir = "/ACMMP";
     bool renamed_outdir = false;
     for (int i = 1; i < argc; ++i) {
@@ -75,7 +75,7 @@ int main(int argc, char **argv) {
         };
         if (a == "-h" || a == "--help") {
             printf("usage: acmmp_main <dense_folder> [--output_dir /ACMMP] [-f|--fuse_thresh 0.3] [--num_consistent_thresh 1]\n"
-                   "                  [--mask_dir DIR] [--image_override DIR] [--device 0] [--gpus N] [--seed N] [--no_fusion] [--reference_flow]\n"
+                   "                  [--mask_dir DIR] [--image_override DIR] [--device 0] [--gpus N] [--seed N] [--staged] [--no_fusion] [--reference_flow]\n"
                    "                  [--force_fusion] [--multi_fusion [/DIR]] [--single_match_penalty N] [-p|--prior]\n");
             return 1;
         } else if (a == "--dense_folder") dense_folder = value("--dense_folder");
@@ -89,6 +89,7 @@ int main(int argc, char **argv) {
         else if (a == "--image_override") image_dir = value("--image_override");
         else if (a == "--device") device = atoi(value("--device"));
         else if (a == "--gpus") gpus = atoi(value("--gpus"));
+        else if (a == "--staged") staged = true;
         else if (a == "--seed") seed = strtoull(value("--seed"), nullptr, 10);
         else if (a == "--no_fusion") fuse = false;
         else if (a == "--reference_flow") ref_flow = true;
@@ -187,9 +188,11 @@ int main(int argc, char **argv) {
             }
             return 0;
         }
-        // --gpus N: the views are sharded over N devices (view v belongs to rank v % N), one host thread and one resident
-        // scan per device; after every stage the depth maps are all-gathered by the library (ncclAllGather on the scans'
-        // streams, communicators from ncclCommInitAll).  N = 1 is the same code without a communicator.
+        // --gpus N: one host thread and one resident scan per device, communicators from ncclCommInitAll.  The scan runs
+        // as a dataflow of (stage, view) tasks (Scan::RunDataflow: rounds of N tasks across stage boundaries, the records
+        // of a round broadcast by the library while the next round computes).  --staged keeps the stage-by-stage loop
+        // (view v belongs to rank v % N, ncclAllGather of the depth maps after every stage); N = 1 always runs that
+        // loop, in the reference's in-place order, without a communicator.
         std::vector<std::unique_ptr<Scan>> scans;
         for (int r = 0; r < gpus; ++r) {
             scans.emplace_back(new Scan(cams, pairs, gpus > 1 ? r : device, r, gpus));
@@ -212,9 +215,18 @@ int main(int argc, char **argv) {
         std::vector<Map<float>> photo_depth(n);
         const int levels = scans[0]->NumLevels();
         std::vector<std::string> errors(gpus);
+        const bool dataflow = gpus > 1 && !staged;
         auto drive = [&](int r) {
             try {
                 Scan &scan = *scans[r];
+                if (dataflow) {
+                    if (r == 0) scan.KeepPhotometric(true);
+                    scan.RunDataflow(seed);
+                    if (r == 0)
+                        for (int i = 0; i < n; ++i) scan.GetPhotometricDepth(i, photo_depth[i]);
+                    scan.Sync();
+                    return;
+                }
                 for (int level = 0; level < levels; ++level) {
                     if (r == 0) printf("Scale: %d\n", levels - 1 - level);
                     scan.BeginLevel(level);
@@ -240,7 +252,8 @@ int main(int argc, char **argv) {
         for (int r = 0; r < gpus; ++r)
             if (!errors[r].empty()) throw std::runtime_error("rank " + std::to_string(r) + ": " + errors[r]);
         // every rank holds every depth map (exchange buffer); normals and costs live on the owner
-        auto get_view = [&](int i, Map<float> *d, Map<float> *nrm, Map<float> *c) { scans[i % gpus]->GetView(i, d, nrm, c); };
+        // (after a dataflow run every rank holds every view's maps)
+        auto get_view = [&](int i, Map<float> *d, Map<float> *nrm, Map<float> *c) { scans[dataflow ? 0 : i % gpus]->GetView(i, d, nrm, c); };
         // acmmp_definitions.cpp:392-401: one folder per reference image
         std::vector<acmmp_camera> cams_out(n);
         for (int i = 0; i < n; ++i) {

@@ -390,6 +390,35 @@ int acmmp_scan_comm_init_all(acmmp_scan *const *scans, int n);
 int acmmp_scan_comm_destroy(acmmp_scan *s);
 int acmmp_scan_all_gather(acmmp_scan *s);
 int acmmp_scan_collect_view(acmmp_scan *s, int view, int root, float *d_normal3, float *d_cost);
+/* The whole scan - every level, every stage (main_ACMMP.cpp:89-176) - as ONE call, scheduled as a dataflow of
+ * (stage, view) tasks instead of stage by stage (csrc/capi_dataflow.cu.inc).  A task needs only the previous stage's
+ * maps of its own view and, for a geometric-consistency run, of its source views (ACMMP.cpp:608-635), so the tasks are
+ * list-scheduled into rounds of `world` tasks that cross stage boundaries: 49 views on 8 GPUs take 37 rounds instead
+ * of 6 stages x 7.  After a round every rank broadcasts the record [depth | normal | cost] it wrote (grouped
+ * ncclBroadcast on a second, high-priority stream, overlapped with the next round's kernels); a task waits only for
+ * the broadcast of the newest round it reads.  Collective: every rank calls it with the same seed after
+ * acmmp_scan_comm_init.  Replaces the acmmp_scan_begin_level / acmmp_scan_run_stage / acmmp_scan_all_gather loop
+ * (do not mix them within one scan pass; acmmp_scan_reset between passes).  Results: those of the staged schedule
+ * with Jacobi geom-1 order, bit for bit.  Afterwards EVERY rank holds the final maps of EVERY view:
+ * acmmp_scan_get_view / acmmp_scan_view_device / acmmp_scan_collect_view serve them locally.
+ * acmmp_scan_keep_photometric(s, 1) before the run keeps a copy of every view's photometric (+ planar prior) depth
+ * of the finest level - the reference's depths.dmb (acmmp_definitions.cpp:392-397), which later stages overwrite - for
+ * acmmp_scan_get_photometric_depth (host buffer, the view's size at the finest level).
+ * acmmp_scan_dataflow_stats: rounds and lag (rounds between a task and the newest round it reads) of the last run.
+ * acmmp_plan_dataflow: the plan alone, on the host (no GPU): task = stage * n_views + view with
+ * stage = level * 3 + {0 photometric+prior, 1 geom-0, 2 geom-1} (stage = level when photometric_only);
+ * task_round / task_rank: n_levels * (photometric_only ? 1 : 3) * n_views entries each. */
+int acmmp_scan_run_dataflow(acmmp_scan *s, uint64_t seed);
+int acmmp_scan_dataflow_stats(const acmmp_scan *s, int *rounds, int *lag);
+/* RunPatchMatch kernel time (init, sweeps, tail, total; CUDA events on the launching stream) of `level` since the last
+ * acmmp_scan_timing / acmmp_scan_level_stats of that level, under either schedule; ncc (may be NULL): the level's NCC
+ * evaluations (init, sweeps) counted by a dataflow run under acmmp_scan_count_ncc; texels_u8 (may be NULL): the
+ * level's texel format.  Waits for the stream. */
+int acmmp_scan_level_stats(acmmp_scan *s, int level, double out_ms[4], uint64_t ncc[2], int *texels_u8);
+int acmmp_scan_keep_photometric(acmmp_scan *s, int on);
+int acmmp_scan_get_photometric_depth(acmmp_scan *s, int view, float *depth);
+int acmmp_plan_dataflow(int n_views, const int32_t *pair_offsets, const int32_t *pair_ids, int n_levels, int photometric_only,
+                        int world, int32_t *task_round, int32_t *task_rank, int32_t *n_rounds, int32_t *lag);
 /* Reduced schedules (before the first level).  single_scale: every view at its (capped) full size from the
  * start, no pyramid (ComputeMultiScaleSettings, acmmp_definitions.cpp:207-243, switched off).
  * photometric_only: the photometric stage is ONE RunPatchMatch per view, without the planar-prior construction
