@@ -312,7 +312,7 @@ def measure_tex_peak(device=0, u8=False):
 STAGE_PHOTO, STAGE_GEOM0, STAGE_GEOM1 = 0, 1, 2
 
 
-def plan_dataflow(pairs, n_levels, world, photometric_only=False):
+def plan_dataflow(pairs, n_levels, world, photometric_only=False, level_cost=None):
     """host only: (task_round, task_rank, n_rounds, lag) of the dataflow schedule; task = stage * n_views + view"""
     lib = L.load()
     n = len(pairs)
@@ -323,7 +323,8 @@ def plan_dataflow(pairs, n_levels, world, photometric_only=False):
     rounds, ranks = np.zeros(T, np.int32), np.zeros(T, np.int32)
     nr, lag = C.c_int32(0), C.c_int32(0)
     I32 = C.POINTER(C.c_int32)
-    rc = lib.acmmp_plan_dataflow(n, off.ctypes.data_as(I32), ids.ctypes.data_as(I32), n_levels, int(photometric_only), world,
+    cost = None if level_cost is None else (C.c_float * n_levels)(*[float(c) for c in level_cost])
+    rc = lib.acmmp_plan_dataflow(n, off.ctypes.data_as(I32), ids.ctypes.data_as(I32), n_levels, int(photometric_only), world, cost,
                                  rounds.ctypes.data_as(I32), ranks.ctypes.data_as(I32), C.byref(nr), C.byref(lag))
     if rc:
         raise RuntimeError("acmmp_plan_dataflow failed (%d)" % rc)
@@ -452,6 +453,15 @@ class Scan:
         ms, ncc, u8 = (C.c_double * 4)(), (C.c_uint64 * 2)(), C.c_int(0)
         self._ck(self._lib.acmmp_scan_level_stats(self._s, level, ms, ncc, C.byref(u8)), "level_stats")
         return {"init_ms": ms[0], "sweeps_ms": ms[1], "tail_ms": ms[2], "total_ms": ms[3], "init": int(ncc[0]), "sweeps": int(ncc[1]), "u8": bool(u8.value)}
+
+    def dataflow_trace(self):
+        """ms after the run's start at which this rank finished each round (sharded scans; empty otherwise)"""
+        cap = max(1, self.dataflow_stats()["rounds"])
+        buf = (C.c_float * cap)()
+        k = self._lib.acmmp_scan_dataflow_trace(self._s, buf, cap)
+        if k < 0:
+            self._ck(k, "dataflow_trace")
+        return [float(buf[i]) for i in range(k)]
 
     def dataflow_stats(self):
         r, lag = C.c_int(0), C.c_int(0)

@@ -290,6 +290,20 @@ def run_ours(args):
             t = scan.level_stats(lv)
             level_tm[lv] = {k: t[k] for k in ("init_ms", "sweeps_ms", "tail_ms", "total_ms")}
             level_u8[lv] = t["u8"]
+    trace = None
+    if dataflow:                        # when each rank finished each round of the last timed step
+        tr = torch.tensor(scan.dataflow_trace(), device=dev, dtype=torch.float32)
+        allr = [torch.zeros_like(tr) for _ in range(world)]
+        dist.all_gather(allr, tr)
+        tr_all = torch.stack(allr).cpu().numpy()                     # (rank, round)
+        durations = np.diff(np.concatenate([np.zeros((world, 1), np.float32), tr_all], 1), axis=1)
+        trace = {"rounds": int(tr_all.shape[1]), "last_round_done_ms": [float(x) for x in tr_all[:, -1]],
+                 "skew_ms_mean": float((tr_all.max(0) - tr_all.min(0)).mean()), "skew_ms_max": float((tr_all.max(0) - tr_all.min(0)).max()),
+                 "note": "ms after the run's start at which a rank had finished round k (compute stream); skew = max - min over ranks per round"}
+        if tr_all.shape[1] <= 64:
+            trace["round_done_ms_rank0"] = [round(float(x), 2) for x in tr_all[0]]
+            trace["round_ms_max_over_ranks"] = [round(float(x), 2) for x in durations.max(0)]
+            trace["round_ms_min_over_ranks"] = [round(float(x), 2) for x in durations.min(0)]
     launches = scan.timing()["launches"] - l0
     hs = scan.host_stats()              # host side of the planar prior in the timed region: triangulation time, and how long the stream waited for it
     level_tm_timed = {lv: dict(t) for lv, t in level_tm.items()}
@@ -410,6 +424,7 @@ def run_ours(args):
                              "reference-formulation flop (NCC x 1538) against the live FP32 FMA peak. traffic = dram bytes per launch from the "
                              "ncu --set full capture in profiles/ (1600x1200 level)"},
         "clocks": clocks.summary(),
+        "dataflow_trace": trace,
         "exchanges_per_step": exchanges_per_step,
         "planar_prior_host": {"delaunay_ms_per_step": hs["prior_host_ms"] / args.steps, "stream_wait_ms_per_step": hs["wait_ms"] / args.steps,
                               "note": "host triangulation of this rank's views (worker threads, overlapped with device work of the next views); "

@@ -374,7 +374,9 @@ int acmmp_scan_set_sequential_geom(acmmp_scan *s, int on);
  * depth maps of the owned views after every stage - the only data that crosses views (ACMMP.cpp:608-635) - with ONE
  * ncclAllGather on the scan's own stream: no host synchronisation, no staging copy.  libnccl.so.2 is loaded with
  * dlopen() on first use (the copy a torch process already holds, else the system's); acmmp_nccl_version() is 0 when
- * it is missing.
+ * it is missing.  Communicators are created with maxCTAs = 4 (ncclCommInitRankConfig; ACMMP_NCCL_MAX_CTAS overrides,
+ * 0 = NCCL's default): a collective spins on its SMs until the slowest rank arrives, and those SMs are lost to the
+ * next task's kernels.
  *   one process per GPU:  rank 0 calls acmmp_nccl_get_unique_id and hands the 128 bytes to the other ranks by any
  *                         means (torch.distributed broadcast, MPI, a file); every rank then calls acmmp_scan_comm_init.
  *   one thread per GPU:   acmmp_scan_comm_init_all(scans, n) (ncclCommInitAll); each thread drives its own scan.
@@ -407,9 +409,14 @@ int acmmp_scan_collect_view(acmmp_scan *s, int view, int root, float *d_normal3,
  * acmmp_scan_dataflow_stats: rounds and lag (rounds between a task and the newest round it reads) of the last run.
  * acmmp_plan_dataflow: the plan alone, on the host (no GPU): task = stage * n_views + view with
  * stage = level * 3 + {0 photometric+prior, 1 geom-0, 2 geom-1} (stage = level when photometric_only);
- * task_round / task_rank: n_levels * (photometric_only ? 1 : 3) * n_views entries each. */
+ * task_round / task_rank: n_levels * (photometric_only ? 1 : 3) * n_views entries each.  Within a round the tasks go
+ * to the ranks with the least WORK so far (rounds are no barriers): level_cost[l] = relative cost of one RunPatchMatch
+ * at level l (NULL: 4^l; the scan uses the level's mean pixel count), a photometric task counts twice. */
 int acmmp_scan_run_dataflow(acmmp_scan *s, uint64_t seed);
 int acmmp_scan_dataflow_stats(const acmmp_scan *s, int *rounds, int *lag);
+/* sharded scans: ms after the start of the last run at which this rank had finished round k (CUDA events on the
+ * compute stream); returns the number of rounds written (0 on an unsharded scan), < 0 on error */
+int acmmp_scan_dataflow_trace(acmmp_scan *s, float *round_done_ms, int capacity);
 /* RunPatchMatch kernel time (init, sweeps, tail, total; CUDA events on the launching stream) of `level` since the last
  * acmmp_scan_timing / acmmp_scan_level_stats of that level, under either schedule; ncc (may be NULL): the level's NCC
  * evaluations (init, sweeps) counted by a dataflow run under acmmp_scan_count_ncc; texels_u8 (may be NULL): the
@@ -418,7 +425,7 @@ int acmmp_scan_level_stats(acmmp_scan *s, int level, double out_ms[4], uint64_t 
 int acmmp_scan_keep_photometric(acmmp_scan *s, int on);
 int acmmp_scan_get_photometric_depth(acmmp_scan *s, int view, float *depth);
 int acmmp_plan_dataflow(int n_views, const int32_t *pair_offsets, const int32_t *pair_ids, int n_levels, int photometric_only,
-                        int world, int32_t *task_round, int32_t *task_rank, int32_t *n_rounds, int32_t *lag);
+                        int world, const float *level_cost, int32_t *task_round, int32_t *task_rank, int32_t *n_rounds, int32_t *lag);
 /* Reduced schedules (before the first level).  single_scale: every view at its (capped) full size from the
  * start, no pyramid (ComputeMultiScaleSettings, acmmp_definitions.cpp:207-243, switched off).
  * photometric_only: the photometric stage is ONE RunPatchMatch per view, without the planar-prior construction

@@ -42,6 +42,10 @@ def check_plan(pairs, levels, world, photometric_only=False):
             if prev_kind != 0:                                                           # readers of the generation (g, v) overwrites
                 for u in users[v]:
                     assert rounds[(g - 1) * n + u] <= r, (g, v, u)
+    # work, not task count, is what is even across ranks: within one costliest task of the mean
+    cost = np.array([(4.0 ** (g // per_level)) * (2.0 if (not photometric_only and g % 3 == 0) else 1.0) for g in range(stages) for _ in range(n)])
+    load = np.array([cost[ranks == r].sum() for r in range(world)])
+    assert load.max() - load.min() <= cost.max() + 1e-6, load
     return n_rounds
 
 
@@ -70,7 +74,7 @@ def test_plan_rejects_bad_arguments():
     lib = L.load()
     off = (C.c_int32 * 3)(0, 1, 2)
     ids = (C.c_int32 * 2)(1, 7)
-    assert lib.acmmp_plan_dataflow(2, off, ids, 1, 0, 2, None, None, None, None) != 0
+    assert lib.acmmp_plan_dataflow(2, off, ids, 1, 0, 2, None, None, None, None, None) != 0
     ids = (C.c_int32 * 2)(1, 0)
-    assert lib.acmmp_plan_dataflow(2, off, ids, 0, 0, 2, None, None, None, None) != 0
-    assert lib.acmmp_plan_dataflow(2, off, ids, 1, 0, 0, None, None, None, None) != 0
+    assert lib.acmmp_plan_dataflow(2, off, ids, 0, 0, 2, None, None, None, None, None) != 0
+    assert lib.acmmp_plan_dataflow(2, off, ids, 1, 0, 0, None, None, None, None, None) != 0
