@@ -13,6 +13,8 @@
 #include <chrono>
 #include <cstring>
 #include <string>
+#include <cuda.h>   // CUtensorMap + enums (types only; the encoder comes from cudaGetDriverEntryPoint)
+
 #include <array>
 #include <vector>
 
@@ -69,12 +71,34 @@ struct PinnedBuf {
 
 // All views of a problem live in ONE layered cudaArray (layer i = view i) behind
 // one texture object, so kernels sample any view through a warp-uniform handle.
+#ifndef ACMMP_BOX_STAGING_DEFAULT
+#define ACMMP_BOX_STAGING_DEFAULT 0
+#endif
+
 struct LayeredImages {
     cudaArray_t arr = nullptr;
     cudaTextureObject_t tex = 0;
     int w = 0, h = 0, layers = 0;
     bool u8 = false;   // R8 unorm texels (integer grey levels, read as normalised float) instead of R32F
+    // R8 only: the same bytes pitch-linear (x, y, layer) under a TMA tensor map, for the sweep kernel's box staging
+    unsigned char *linear = nullptr;
+    CUtensorMap map;
+    bool has_map = false;
 };
+
+// cuTensorMapEncodeTiled through the runtime (no link against libcuda); null when the driver lacks it
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        (void)cudaGetLastError();
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
 
 }  // namespace
 
@@ -103,6 +127,10 @@ struct acmmp_ctx {
     // problem holds integer grey levels 0..255 (bit-identical results, ncc.cuh), else float texels
     int tex_format = ACMMP_TEX_R32F;
     bool ext_tex_u8 = false;
+    CUtensorMap ext_map;           // copy of the caller's tensor map over the R8 layers (box staging)
+    bool ext_has_map = false;
+    int ext_w = 0, ext_h = 0;
+    int box_staging = -1;          // acmmp_set_box_staging: -1 = ACMMP_BOX_STAGING from the environment (default off)
     DevBuf stage_u8, u8_flag;
     // resident path: all views of a scan live in one layered array owned by the scan;
     // a problem then only names layers (no per-problem upload)
@@ -164,6 +192,7 @@ int bind_device(acmmp_ctx *ctx) {
 void destroy_views(LayeredImages &v) {
     if (v.tex) cudaDestroyTextureObject(v.tex);
     if (v.arr) cudaFreeArray(v.arr);
+    if (v.linear) cudaFree(v.linear);
     v = LayeredImages();
 }
 
@@ -193,11 +222,28 @@ cudaError_t make_layered(LayeredImages &v, int w, int h, int layers, bool u8) {
     v.h = h;
     v.layers = layers;
     v.u8 = u8;
+    // linear copy + tensor map (box kBoxW x kBoxH x 1); rows must be a multiple of 16 bytes
+    if (u8 && w % 16 == 0 && w >= acmmp::kBoxW && h >= acmmp::kBoxH && encode_tiled_fn()) {
+        if (cudaMalloc(&v.linear, (size_t)w * h * layers) != cudaSuccess) {
+            (void)cudaGetLastError();
+            v.linear = nullptr;
+            return cudaSuccess;
+        }
+        const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)layers};
+        const cuuint64_t strides[2] = {(cuuint64_t)w, (cuuint64_t)w * h};
+        const cuuint32_t box[3] = {acmmp::kBoxW, acmmp::kBoxH, 1}, estr[3] = {1, 1, 1};
+        v.has_map = encode_tiled_fn()(&v.map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, v.linear, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                      CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    }
     return cudaSuccess;
 }
 
 // bytes of one layer -> layer `layer` of an R8 array
 cudaError_t copy_layer_u8(const LayeredImages &v, int layer, const uint8_t *d_src, cudaStream_t st) {
+    if (v.linear) {
+        cudaError_t e = cudaMemcpyAsync(v.linear + (size_t)layer * v.w * v.h, d_src, (size_t)v.w * v.h, cudaMemcpyDeviceToDevice, st);
+        if (e != cudaSuccess) return e;
+    }
     cudaMemcpy3DParms cp;
     memset(&cp, 0, sizeof cp);
     cp.srcPtr = make_cudaPitchedPtr(const_cast<uint8_t *>(d_src), (size_t)v.w, v.w, v.h);
@@ -361,13 +407,19 @@ int problem_common(acmmp_ctx *ctx, int n, const acmmp_camera *cams) {
 // resident path: the views already sit in layers of `tex` (owned by the caller);
 // ref_image = row-major reference image on the device (borrowed)
 int set_problem_resident(acmmp_ctx *ctx, int n, const acmmp_camera *cams, cudaTextureObject_t tex, bool tex_u8,
-                         const float *ref_image, const int *layers) {
+                         const float *ref_image, const int *layers, const LayeredImages *views = nullptr) {
     if (n < 2 || n - 1 > ACMMP_MAX_SRC_VIEWS) return fail(ctx, ACMMP_ERR_INVALID, "need 1 reference + 1..%d source views, got n=%d", ACMMP_MAX_SRC_VIEWS, n);
     if (bind_device(ctx)) return ACMMP_ERR_CUDA;
     ctx->n = n;
     ctx->cams.assign(cams, cams + n);
     ctx->ext_tex = tex;
     ctx->ext_tex_u8 = tex_u8;
+    ctx->ext_has_map = views && views->has_map && tex_u8;
+    if (ctx->ext_has_map) {
+        ctx->ext_map = views->map;
+        ctx->ext_w = views->w;
+        ctx->ext_h = views->h;
+    }
     ctx->ext_ref_image = ref_image;
     ctx->layers.assign(layers, layers + n);
     return problem_common(ctx, n, cams);
@@ -548,6 +600,7 @@ int acmmp_set_problem(acmmp_ctx *ctx, int n, const acmmp_camera *cams, const flo
     }
     ctx->ext_tex = 0;
     ctx->ext_tex_u8 = false;
+    ctx->ext_has_map = false;
     ctx->ext_ref_image = nullptr;
     ctx->layers.resize(n);
     for (int i = 0; i < n; ++i) ctx->layers[i] = i;

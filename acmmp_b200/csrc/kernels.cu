@@ -367,14 +367,18 @@ cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st) {
     a.compat = L.compat;
     a.wave_lo = L.wave_lo; a.wave_hi = L.wave_hi; a.ref_grid_x = L.ref_grid_x;
     a.ncc_counter = L.ncc_counter;
-    const size_t smem = sweep_smem_bytes(L.nsrc);
+    const bool boxes = L.tex_u8 && L.views_map != nullptr && L.layer_w >= kBoxW && L.layer_h >= kBoxH;
+    if (boxes) memcpy(&a.views_map, L.views_map, sizeof a.views_map);
+    else memset(&a.views_map, 0, sizeof a.views_map);
+    a.layer_w = L.layer_w; a.layer_h = L.layer_h;
+    const size_t smem = sweep_smem_bytes(L.nsrc, boxes);
+    auto kernel = boxes ? sweep_kernel<true, true> : (L.tex_u8 ? sweep_kernel<true, false> : sweep_kernel<false, false>);
     // per-device attribute: see launch_init
     if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(L.tex_u8 ? sweep_kernel<true> : sweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    if (L.tex_u8) sweep_kernel<true><<<grid2(L.W, L.H, kTileW, kTileH), kSweepThreads, smem, st>>>(a);
-    else sweep_kernel<false><<<grid2(L.W, L.H, kTileW, kTileH), kSweepThreads, smem, st>>>(a);
+    kernel<<<grid2(L.W, L.H, kTileW, kTileH), kSweepThreads, smem, st>>>(a);
     return cudaGetLastError();
 }
 

@@ -7,6 +7,9 @@
 
 namespace acmmp {
 
+// box staging of the sweep kernel (ncc.cuh): bytes per box row / rows per box
+constexpr int kBoxW = 64, kBoxH = 32;
+
 struct PairConst;
 struct RefConst;
 
@@ -53,6 +56,9 @@ struct SweepLaunch {
     int geom_consistency, planar_prior, hierarchy, compat;
     int wave_lo, wave_hi, ref_grid_x;   // wave emulation (sweep_kernel.cuh); wave_hi == 0: off
     unsigned long long *ncc_counter;   // nullable; 4096 slots
+    // box staging (ncc.cuh): host copy of the tensor map over the R8 layers as linear bytes, or null; layer size
+    const void *views_map;
+    int layer_w, layer_h;
 };
 
 // h_cams / h_depth_maps are HOST arrays (of device pointers for the depth maps): passed as a kernel argument

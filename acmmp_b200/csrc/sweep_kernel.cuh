@@ -28,6 +28,8 @@
 //    the other, no copies), which is deterministic and what the reference does
 //    whenever the neighbour has not finished yet.
 #pragma once
+#include <cuda.h>   // CUtensorMap (type only)
+
 #include "common.cuh"
 #include "geometry.cuh"
 #include "ncc.cuh"
@@ -85,8 +87,32 @@ struct SweepArgs {
     // same-colour neighbours in blocks < wave_lo from the output buffers.
     int wave_lo, wave_hi, ref_grid_x;
     unsigned long long *ncc_counter;   // optional instrumentation: kNccCounterSlots slots, NCC evaluations issued
+    // sweep_kernel<true, true> only: the R8 layers as a pitch-linear (x, y, layer) byte tensor for TMA (box staging, ncc.cuh)
+    CUtensorMap views_map;
+    int layer_w, layer_h;
 };
 constexpr int kNccCounterSlots = 4096;
+
+// mbarrier / TMA primitives of the box staging
+ACMMP_DEV uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+ACMMP_DEV void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+ACMMP_DEV void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+ACMMP_DEV void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n.reg .pred p;\nWAIT_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(smem_addr(bar)),
+        "r"(parity)
+        : "memory");
+}
+ACMMP_DEV void tma_load_box(void *dst, const CUtensorMap *map, int x, int y, int layer, uint64_t *bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(smem_addr(dst)),
+                 "l"(map), "r"(x), "r"(y), "r"(layer), "r"(smem_addr(bar))
+                 : "memory");
+}
 
 // Per-pixel shared-memory block.  nsrc-sized arrays follow the fixed part.
 struct GroupSmemFixed {
@@ -98,12 +124,18 @@ ACMMP_DEV size_t group_smem_floats(int nsrc) {
     return (size_t)nsrc * 8 + (size_t)6 * nsrc + nsrc;
 }
 
-__host__ __device__ inline size_t sweep_smem_bytes(int nsrc) {
+__host__ __device__ inline size_t sweep_smem_bytes(int nsrc, bool boxes = false) {
     size_t per_group = sizeof(GroupSmemFixed) + ((size_t)nsrc * 8 + (size_t)6 * nsrc + nsrc) * sizeof(float);
     per_group = (per_group + 15) & ~(size_t)15;
     size_t pairs = ((size_t)nsrc * sizeof(PairConst) + 15) & ~(size_t)15;
     size_t rc = (sizeof(RefConst) + 15) & ~(size_t)15;
-    return pairs + rc + per_group * kGroupsPerCta;
+    size_t total = pairs + rc + per_group * kGroupsPerCta;
+    if (boxes) {   // [mbarrier 16 B][box origins nsrc x 8 B] -> 128-byte boundary -> nsrc boxes
+        total += 16 + (size_t)nsrc * 8;
+        total = (total + 127) & ~(size_t)127;
+        total += (size_t)nsrc * kBoxW * kBoxH;
+    }
+    return total;
 }
 
 // group-scoped shuffle helpers

@@ -59,6 +59,11 @@ class ACMMP:
         0 = off, the deterministic default).  include/acmmp_b200.h: acmmp_set_wave_emulation."""
         _check(self._ctx, self._lib.acmmp_set_wave_emulation(self._ctx, int(resident_blocks)), "SetWaveEmulation")
 
+    def SetBoxStaging(self, on):
+        """TMA box staging of the sweep kernel on R8 problems: True / False, None = the process default
+        (include/acmmp_b200.h: acmmp_set_box_staging); results do not depend on it"""
+        _check(self._ctx, self._lib.acmmp_set_box_staging(self._ctx, -1 if on is None else int(bool(on))), "SetBoxStaging")
+
     def SetTextureFormat(self, fmt):
         """L.TEX_R32F (default) or L.TEX_AUTO: R8 texels for the next problems whose images all hold
         integer grey levels (bit-identical samples, a quarter of the texture footprint)."""
@@ -437,6 +442,10 @@ class Scan:
         """the whole scan (all levels, all stages) as a dataflow of (stage, view) tasks; collective on a sharded scan.
         Afterwards every rank holds every view's final maps (get_view / view_device)."""
         self._ck(self._lib.acmmp_scan_run_dataflow(self._s, C.c_uint64(seed)), "run_dataflow")
+
+    def set_box_staging(self, on):
+        """TMA box staging of the sweep kernel on R8 levels: True / False, None = the process default"""
+        self._ck(self._lib.acmmp_scan_set_box_staging(self._s, -1 if on is None else int(bool(on))), "set_box_staging")
 
     def keep_photometric(self, on=True):
         self._ck(self._lib.acmmp_scan_keep_photometric(self._s, int(bool(on))), "keep_photometric")

@@ -69,7 +69,7 @@ EXPORTS = [
     "acmmp_scan_set_prior_maps", "acmmp_prior_planes_from_maps", "acmmp_seeded_last_error",
     "acmmp_scan_create", "acmmp_scan_destroy", "acmmp_scan_last_error", "acmmp_scan_set_image", "acmmp_scan_set_image_u8",
     "acmmp_scan_set_shard", "acmmp_scan_set_texture_format", "acmmp_scan_level_is_u8", "acmmp_scan_set_sequential_geom", "acmmp_scan_set_schedule", "acmmp_nccl_version", "acmmp_nccl_get_unique_id", "acmmp_scan_comm_init",
-    "acmmp_scan_comm_init_all", "acmmp_scan_comm_destroy", "acmmp_scan_all_gather", "acmmp_scan_collect_view", "acmmp_scan_run_dataflow", "acmmp_scan_dataflow_stats", "acmmp_scan_dataflow_trace", "acmmp_plan_dataflow", "acmmp_scan_keep_photometric", "acmmp_scan_level_stats", "acmmp_scan_get_photometric_depth", "acmmp_scan_num_levels", "acmmp_scan_begin_level",
+    "acmmp_scan_comm_init_all", "acmmp_scan_comm_destroy", "acmmp_scan_all_gather", "acmmp_scan_collect_view", "acmmp_scan_run_dataflow", "acmmp_scan_dataflow_stats", "acmmp_scan_dataflow_trace", "acmmp_plan_dataflow", "acmmp_scan_keep_photometric", "acmmp_set_box_staging", "acmmp_scan_set_box_staging", "acmmp_scan_level_stats", "acmmp_scan_get_photometric_depth", "acmmp_scan_num_levels", "acmmp_scan_begin_level",
     "acmmp_scan_run_stage", "acmmp_scan_exchange", "acmmp_scan_view_size", "acmmp_scan_get_view", "acmmp_scan_view_device",
     "acmmp_scan_timing", "acmmp_scan_sync", "acmmp_scan_reset", "acmmp_scan_host_stats", "acmmp_scan_mark", "acmmp_scan_elapsed",
 ]
@@ -162,6 +162,8 @@ def load():
     lib.acmmp_scan_run_dataflow.argtypes = [vp, C.c_uint64]
     lib.acmmp_scan_level_stats.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.POINTER(C.c_int)]
     lib.acmmp_scan_dataflow_trace.argtypes = [vp, C.POINTER(C.c_float), C.c_int]
+    lib.acmmp_set_box_staging.argtypes = [vp, C.c_int]
+    lib.acmmp_scan_set_box_staging.argtypes = [vp, C.c_int]
     lib.acmmp_scan_keep_photometric.argtypes = [vp, C.c_int]
     lib.acmmp_scan_get_photometric_depth.argtypes = [vp, C.c_int, vp]
     lib.acmmp_scan_dataflow_stats.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]

@@ -361,6 +361,14 @@ int acmmp_scan_set_shard(acmmp_scan *s, int rank, int world);
  * view is resized and every image holds integer grey levels); call before acmmp_scan_begin_level.
  * acmmp_scan_level_is_u8: what the current level uses. */
 int acmmp_scan_set_texture_format(acmmp_scan *s, int format);
+/* Box staging of the sweep kernel on R8 levels (north_star: "source-view patches staged in shared memory via TMA
+ * tiles"): per 16 x 4 tile and source view a 64 x 32-byte box of the view's layer goes to shared memory by
+ * cp.async.bulk.tensor, placed where the tile's centre lands under its current plane; taps whose texels lie inside are
+ * filtered from it with the texture unit's own 1/256 weights (bit-identical on 8-bit texels), every other tap goes
+ * through the unit.  1 = on, 0 = off, -1 = the process default (environment ACMMP_BOX_STAGING, else the build's).
+ * Results do not depend on the setting. */
+int acmmp_set_box_staging(acmmp_ctx *ctx, int on);
+int acmmp_scan_set_box_staging(acmmp_scan *s, int on);
 int acmmp_scan_level_is_u8(const acmmp_scan *s);
 /* Order of the second geometric-consistency pass.  1 = the reference's in-place
  * order dependence (ProcessProblem rewrites depths_geom.dmb, so geom-1 of view i reads
