@@ -15,6 +15,8 @@
 #include <string>
 #include <cuda.h>   // CUtensorMap + enums (types only; the encoder comes from cudaGetDriverEntryPoint)
 
+#include <nvtx3/nvToolsExt.h>   // header-only; ranges cost nothing unless a tool is attached
+
 #include <array>
 #include <vector>
 
@@ -46,6 +48,30 @@ struct DevBuf {
         cap = 0;
     }
     template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+// NVTX range over a scope: "acmmp/<what>" on the issuing thread (ncu --nvtx --nvtx-include "acmmp/photo L1/" ...,
+// or any NVTX-aware timeline tool); names the stage, level and view the enclosed launches belong to
+struct NvtxRange {
+    explicit NvtxRange(const char *fmt, ...) {
+        char buf[96];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof buf, fmt, ap);
+        va_end(ap);
+        nvtxRangePushA(buf);
+    }
+    NvtxRange(const NvtxRange &) = delete;
+    NvtxRange &operator=(const NvtxRange &) = delete;
+    ~NvtxRange() { nvtxRangePop(); }
+};
+
+// a device buffer that frees itself: the stand-alone operators return from the middle on errors
+struct ScopedBuf : DevBuf {
+    ScopedBuf() = default;
+    ScopedBuf(const ScopedBuf &) = delete;
+    ScopedBuf &operator=(const ScopedBuf &) = delete;
+    ~ScopedBuf() { release(); }
 };
 
 // page-locked host staging (async D2H / H2D without implicit stream syncs)

@@ -274,7 +274,7 @@ private:
         std::string err;
         bool ok = false;
         for (const char *ext : {".jpg", ".pgm", ".ppm", ".raw"})
-            if (ReadImage(dense_folder + "/images" + name + ext, raw, &err, false, device_)) {
+            if (ReadImageCached(dense_folder + "/images" + name + ext, raw, &err, false, device_)) {
                 ok = true;
                 break;
             }

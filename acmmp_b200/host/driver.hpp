@@ -22,7 +22,7 @@ inline std::string ImagePath(const std::string &dense_folder, int id, const char
 inline bool ReadGreyImage(const std::string &dense_folder, int id, Map<uint8_t> &raw, int device) {
     std::string err;
     for (const char *ext : {".jpg", ".pgm", ".ppm", ".raw"})
-        if (ReadImage(ImagePath(dense_folder, id, ext), raw, &err, false, device)) return true;
+        if (ReadImageCached(ImagePath(dense_folder, id, ext), raw, &err, false, device)) return true;
     return false;
 }
 

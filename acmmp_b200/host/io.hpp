@@ -11,8 +11,13 @@
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <list>
+#include <map>
+#include <mutex>
 #include <string>
 #include <vector>
+
+#include <sys/stat.h>
 
 #include "../../include/acmmp_b200.h"
 #ifdef ACMMP_IO_WITH_PNG
@@ -267,6 +272,91 @@ inline bool ReadImage(const std::string &path, Map<uint8_t> &out, std::string *e
     fclose(f);
     if (!ok && err && err->empty()) *err = path + ": truncated image";
     return ok;
+}
+
+// Content cache of decoded images.  The reference decodes every view of every problem again at every stage
+// (InputInitialization, ACMMP.cpp:534-564: 49 x 11 x 6 cv::imread calls on the headline scan); its per-view flow
+// (host/driver.hpp: ProcessProblem, JointBilateralUpsampling, ComputeMultiScaleSettings) goes through this cache
+// instead: one decode per file and colour mode, keyed by path, validated against the file's size and modification
+// time, least-recently-used entries dropped beyond the byte budget (ACMMP_IMAGE_CACHE_MB, default 4096; 0 = off).
+// The resident schedule (class Scan) needs none: it holds every decoded view in HBM for the whole scan.
+class ImageCache {
+  public:
+    struct Stats { uint64_t hits = 0, misses = 0, evictions = 0; size_t bytes = 0; };
+    static ImageCache &Instance() {
+        static ImageCache c;
+        return c;
+    }
+    bool Read(const std::string &path, Map<uint8_t> &out, std::string *err, bool color, int device) {
+        struct stat st;
+        if (budget_ == 0 || stat(path.c_str(), &st) != 0) return ReadImage(path, out, err, color, device);
+        const std::string key = path + (color ? "#c" : "#g");
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            auto it = index_.find(key);
+            if (it != index_.end()) {
+                Entry &e = *it->second;
+                if (e.size == st.st_size && e.mtime_s == st.st_mtim.tv_sec && e.mtime_ns == st.st_mtim.tv_nsec) {
+                    lru_.splice(lru_.begin(), lru_, it->second);
+                    out = e.image;
+                    stats_.hits++;
+                    return true;
+                }
+                stats_.bytes -= e.image.data.size();   // the file changed: decode again
+                lru_.erase(it->second);
+                index_.erase(it);
+            }
+        }
+        if (!ReadImage(path, out, err, color, device)) return false;
+        std::lock_guard<std::mutex> lock(mu_);
+        stats_.misses++;
+        if (out.data.size() > budget_ || index_.count(key)) return true;
+        lru_.push_front(Entry{key, out, st.st_size, st.st_mtim.tv_sec, st.st_mtim.tv_nsec});
+        index_[key] = lru_.begin();
+        stats_.bytes += out.data.size();
+        while (stats_.bytes > budget_ && lru_.size() > 1) {
+            stats_.bytes -= lru_.back().image.data.size();
+            index_.erase(lru_.back().key);
+            lru_.pop_back();
+            stats_.evictions++;
+        }
+        return true;
+    }
+    Stats stats() {
+        std::lock_guard<std::mutex> lock(mu_);
+        return stats_;
+    }
+    void SetBudget(size_t bytes) {
+        std::lock_guard<std::mutex> lock(mu_);
+        budget_ = bytes;
+        while (stats_.bytes > budget_ && !lru_.empty()) {
+            stats_.bytes -= lru_.back().image.data.size();
+            index_.erase(lru_.back().key);
+            lru_.pop_back();
+            stats_.evictions++;
+        }
+    }
+
+  private:
+    struct Entry {
+        std::string key;
+        Map<uint8_t> image;
+        off_t size;
+        time_t mtime_s;
+        long mtime_ns;
+    };
+    ImageCache() {
+        const char *e = getenv("ACMMP_IMAGE_CACHE_MB");
+        budget_ = (size_t)(e ? atoll(e) : 4096) << 20;
+    }
+    std::mutex mu_;
+    std::list<Entry> lru_;
+    std::map<std::string, std::list<Entry>::iterator> index_;
+    size_t budget_ = 0;
+    Stats stats_;
+};
+inline bool ReadImageCached(const std::string &path, Map<uint8_t> &out, std::string *err = nullptr, bool color = true, int device = 0) {
+    return ImageCache::Instance().Read(path, out, err, color, device);
 }
 
 // cv::resize(src, dst, Size(dw, dh), 0, 0, INTER_LINEAR) on 8-bit images, as RunFusion applies it to the colour

@@ -46,6 +46,35 @@ int main(int argc, char **argv) {
         printf("resized=%d,%d,%d\n", out.rows, out.cols, out.channels);
         return 0;
     }
+    if (argc >= 4 && std::string(argv[1]) == "--cache") {   // io_selftest --cache a.pgm b.pgm: the decoded-image content cache
+        ImageCache &cache = ImageCache::Instance();
+        Map<uint8_t> a1, a2, b1, a3;
+        std::string err;
+        if (!ReadImageCached(argv[2], a1, &err, false) || !ReadImageCached(argv[2], a2, &err, false) || !ReadImageCached(argv[3], b1, &err, false)) {
+            fprintf(stderr, "%s\n", err.c_str());
+            return 16;
+        }
+        ImageCache::Stats st = cache.stats();
+        printf("after_three_reads=%llu,%llu,%zu same=%d\n", (unsigned long long)st.hits, (unsigned long long)st.misses, st.bytes, a1.data == a2.data ? 1 : 0);
+        // rewrite the first file with other content (and another size): the entry must not be served again
+        FILE *f = fopen(argv[2], "wb");
+        if (!f) return 13;
+        fprintf(f, "P5\n2 1\n255\n");
+        fputc(7, f);
+        fputc(9, f);
+        fclose(f);
+        if (!ReadImageCached(argv[2], a3, &err, false)) return 16;
+        st = cache.stats();
+        printf("after_rewrite=%llu,%llu,%zu first=%d,%d,%d\n", (unsigned long long)st.hits, (unsigned long long)st.misses, st.bytes, a3.rows, a3.cols, (int)a3.data[0]);
+        cache.SetBudget(b1.data.size());   // room for one image: the least recently used one goes
+        st = cache.stats();
+        printf("after_budget=%llu,%zu\n", (unsigned long long)st.evictions, st.bytes);
+        Map<uint8_t> b2;
+        if (!ReadImageCached(argv[3], b2, &err, false)) return 16;
+        st = cache.stats();
+        printf("final=%llu,%llu\n", (unsigned long long)st.hits, (unsigned long long)st.misses);
+        return 0;
+    }
     if (argc >= 4 && std::string(argv[1]) == "--dmb") {   // io_selftest --dmb file depth|normal|any: 0 if accepted
         Map<float> m;
         const std::string kind = argv[3];

@@ -275,8 +275,12 @@ int acmmp_timing_collect(acmmp_ctx *ctx, double out_ms[4], int *runs);
 /* ---- JBU ---------------------------------------------------------------------
  * RunJBU / JBU::CudaRun / JBU_cu (ACMMP.cpp:1022-1087, ACMMP.cu:1458-1549):
  * joint bilateral upsample of a (sw x sh) depth map to (w x h) guided by the
- * (w x h) image.  Returns 1 (and writes nothing) when the integer scale is 1,
- * like the reference's early-out. */
+ * (w x h) image.  Returns ACMMP_JBU_NOTHING_TO_DO (+1; error codes are negative) and
+ * writes nothing when the integer scale is 1, like the reference's early-out
+ * (ACMMP.cpp:1032-1035).  A whole scan whose levels have the same size is refused by
+ * acmmp_scan_begin_level / acmmp_scan_run_dataflow (ACMMP_ERR_STATE): the reference then
+ * keeps the previous scale's photometric depths.dmb, a case this schedule does not model. */
+#define ACMMP_JBU_NOTHING_TO_DO 1
 int acmmp_jbu_depth(int device, const float *image, int w, int h,
                     const float *depth, int sw, int sh, float *out);
 

@@ -136,3 +136,19 @@ def test_dmb_reader_rejects_bad_headers(tmp_path):
     assert run(write("ch.dmb", [1, 3, 4, 2], np.zeros(24, np.float32).tobytes()), "any") != 0
     assert run(write("type.dmb", [2, 3, 4, 1], np.zeros(12, np.float32).tobytes()), "any") != 0
     assert run(write("short.dmb", [1, 3, 4, 1], np.zeros(5, np.float32).tobytes()), "any") != 0
+
+
+def test_decoded_image_content_cache(tmp_path):
+    """ImageCache (host/io.hpp): one decode per file, validated by size + mtime, LRU under a byte budget"""
+    a, b = tmp_path / "a.pgm", tmp_path / "b.pgm"
+    rng = np.random.default_rng(0)
+    for path, (h, w) in ((a, (30, 40)), (b, (20, 50))):
+        with open(path, "wb") as f:
+            f.write(b"P5\n%d %d\n255\n" % (w, h) + rng.integers(0, 256, (h, w), dtype=np.uint8).tobytes())
+    out = subprocess.run([EXE, "--cache", str(a), str(b)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    lines = dict(l.split("=", 1) for l in out.stdout.strip().splitlines())
+    assert lines["after_three_reads"] == "1,2,%d same=1" % (30 * 40 + 20 * 50)       # second read of a: a hit
+    assert lines["after_rewrite"] == "1,3,%d first=1,2,7" % (2 + 20 * 50)             # changed file: decoded again
+    assert lines["after_budget"] == "1,2"                                             # the least recently used entry (b) was dropped
+    assert lines["final"] == "1,4"                                                    # ... so b is decoded again
