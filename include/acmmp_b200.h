@@ -332,9 +332,10 @@ int acmmp_tex_sample_u8(int device, const float *image, int width, int height, c
  *
  * Sharding: rank r of `world` owns the views v with v % world == r and runs
  * ProcessProblem (acmmp_definitions.cpp:245-403) for them only.  Only depth
- * maps cross views (ACMMP.cpp:608-635); after every stage the caller
- * all-gathers the exchange buffer (acmmp_scan_exchange) across ranks - the
- * library itself never communicates.
+ * maps cross views (ACMMP.cpp:608-635); after every stage the ranks all-gather
+ * the exchange buffer: acmmp_scan_all_gather (NCCL inside the library, section
+ * "multi-GPU" below), or a caller's own transport over acmmp_scan_exchange.
+ * acmmp_scan_run_dataflow runs the whole sharded scan without the stage barrier.
  *
  * levels: ComputeMultiScaleSettings (acmmp_definitions.cpp:207-243); level 0 is
  * the coarsest.  Stages per level, in order:
