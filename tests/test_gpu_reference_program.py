@@ -52,6 +52,15 @@ def test_reference_program_and_product_agree(tmp_path, size):
         print("view %d: acc<1%% ref %.4f ours %.4f, depth within 0.1%% of each other %.4f" % (i, acc_ref, acc_our, agree))
         assert acc_ref >= 0.9 and abs(acc_our - acc_ref) <= 0.01
         assert agree >= (0.93 if w < 1000 else 0.97)
-    # fused clouds: different random streams and the reference's races move individual pixels; the
-    # count is a scene-level quantity (measured on B200: +0.40 % at 320x240, +0.08 % at 1280x960)
-    assert abs(len(pts) - len(ref_xyz)) <= 0.01 * len(ref_xyz), (len(pts), len(ref_xyz))
+    # fused clouds: different random streams and the reference's races move individual pixels; the count is a
+    # scene-level quantity.  Yardstick: the reference program against ITSELF with another seed, on the same folder.
+    dense2 = str(tmp_path / "dense2")
+    refbind.write_dense_folder(dense2, sc["cams"], sc["images"], sc["pairs"])
+    refbind.full_run(dense2, seed=100)
+    ref2_xyz, _ = refbind.read_ply(os.path.join(dense2, "ACMMP", "ACMMP_model.ply"))
+    d_our, d_ref = abs(len(pts) - len(ref_xyz)) / len(ref_xyz), abs(len(ref2_xyz) - len(ref_xyz)) / len(ref_xyz)
+    print("fused points %dx%d: reference %d, reference (other seed) %d (%.3f %%), product %d (%.3f %%)"
+          % (w, h, len(ref_xyz), len(ref2_xyz), 100 * d_ref, len(pts), 100 * d_our))
+    # north_star: +-0.1 % at the two-scale size (measured on B200: 0.08 %), never further away than the reference is
+    # from itself plus that; the tiny one-scale case is noisier (0.40 %)
+    assert d_our <= (0.001 if w >= 1000 else 0.006) + d_ref, (len(pts), len(ref_xyz), len(ref2_xyz))
