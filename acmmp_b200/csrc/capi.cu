@@ -50,8 +50,9 @@ struct DevBuf {
     template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
-// NVTX range over a scope: "acmmp/<what>" on the issuing thread (ncu --nvtx --nvtx-include "acmmp/photo L1/" ...,
-// or any NVTX-aware timeline tool); names the stage, level and view the enclosed launches belong to
+// NVTX push/pop range over a scope on the issuing thread, named "acmmp:<task>:L<level>:v<view>" (no '/' or spaces:
+// ncu's filter syntax uses them): `ncu --nvtx --nvtx-include "acmmp:geom1:L1:v1/" ...` profiles exactly the launches of
+// that task; any NVTX-aware timeline tool shows the schedule
 struct NvtxRange {
     explicit NvtxRange(const char *fmt, ...) {
         char buf[96];
