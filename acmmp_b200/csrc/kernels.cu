@@ -353,6 +353,10 @@ cudaError_t launch_init(const InitLaunch &L, cudaStream_t st) {
     return cudaGetLastError();
 }
 
+// ACMMP_SWEEP_MAX_BLOCKS=3 (compile time) keeps the three-CTA configuration everywhere (variant timing)
+#ifndef ACMMP_SWEEP_MAX_BLOCKS
+#define ACMMP_SWEEP_MAX_BLOCKS 4
+#endif
 cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st) {
     SweepArgs a;
     a.planes_other = L.planes_other; a.costs_other = L.costs_other;
@@ -372,7 +376,11 @@ cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st) {
     else memset(&a.views_map, 0, sizeof a.views_map);
     a.layer_w = L.layer_w; a.layer_h = L.layer_h;
     const size_t smem = sweep_smem_bytes(L.nsrc, boxes);
-    auto kernel = boxes ? sweep_kernel<true, true> : (L.tex_u8 ? sweep_kernel<true, false> : sweep_kernel<false, false>);
+    // four CTAs per SM when their shared memory fits (1 KB per CTA is reserved by the system), else three
+    const bool four = !boxes && 4 * (smem + 1024) <= (size_t)228 * 1024 && ACMMP_SWEEP_MAX_BLOCKS >= 4;
+    auto kernel = boxes ? sweep_kernel<true, true, 3>
+                        : (L.tex_u8 ? (four ? sweep_kernel<true, false, 4> : sweep_kernel<true, false, 3>)
+                                    : (four ? sweep_kernel<false, false, 4> : sweep_kernel<false, false, 3>));
     // per-device attribute: see launch_init
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

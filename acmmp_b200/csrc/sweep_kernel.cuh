@@ -118,6 +118,18 @@ ACMMP_DEV void tma_load_box(void *dst, const CUtensorMap *map, int x, int y, int
 struct GroupSmemFixed {
     RefPatch rp;
 };
+// sweep_kernel: the five refinement candidates of the pixel live here between their generation and the decision, so
+// that they do not occupy 25 registers across the NCC loop (which both passes share)
+struct SweepGroupSmem {
+    RefPatch rp;
+    // operands of the shared NCC loop: planes[lane] = the candidate of checkerboard arm `lane` (pass 0),
+    // planes[8 + i] = refinement candidate i (pass 1)
+    float4 planes[13];
+    float4 plane_c;                          // the pixel's own plane before the half-sweep
+    float4 plane_now, live_plane, prior;     // parked across the second pass (lane 0 writes, every lane reads back)
+    float cand_depth[8];
+    float scal[8];                           // parked scalars: cost_now, live_cost, depth_now, restricted_cost, depth_prior
+};
 
 ACMMP_DEV size_t group_smem_floats(int nsrc) {
     // cm[nsrc][8] + task costs [6][nsrc] + probs[nsrc]
@@ -125,7 +137,7 @@ ACMMP_DEV size_t group_smem_floats(int nsrc) {
 }
 
 __host__ __device__ inline size_t sweep_smem_bytes(int nsrc, bool boxes = false) {
-    size_t per_group = sizeof(GroupSmemFixed) + ((size_t)nsrc * 8 + (size_t)6 * nsrc + nsrc) * sizeof(float);
+    size_t per_group = sizeof(SweepGroupSmem) + ((size_t)nsrc * 8 + (size_t)6 * nsrc + nsrc) * sizeof(float);
     per_group = (per_group + 15) & ~(size_t)15;
     size_t pairs = ((size_t)nsrc * sizeof(PairConst) + 15) & ~(size_t)15;
     size_t rc = (sizeof(RefConst) + 15) & ~(size_t)15;

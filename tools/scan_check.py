@@ -65,4 +65,10 @@ for level in range(nl):
             acc.append(round(float((err[8:-8, 8:-8] < 0.01).mean()), 4))
         print(json.dumps({"level": level, "stage": names[st], "wall_s": round(wall, 3), "kernel_ms": round(tm["total_ms"], 1),
                           "sweeps_ms": round(tm["sweeps_ms"], 1), "runs": tm["runs"], "prior_host_ms": round(hs["prior_host_ms"], 1), "wait_ms": round(hs["wait_ms"], 1), "acc<1%": acc, "size": list(d.shape)}), flush=True)
+import zlib
+crc = 0
+for v in range(args.views):
+    d, n, c = scan.get_view(v)
+    crc = zlib.crc32(c.tobytes(), zlib.crc32(n.tobytes(), zlib.crc32(d.tobytes(), crc)))
+print("crc", crc)
 print("total wall s", round(time.time() - t_all, 2), "views/s", round(args.views / (time.time() - t_all), 3))
