@@ -146,6 +146,7 @@ struct acmmp_ctx {
     int compat = ACMMP_COMPAT_REF_SM100;
     int split = -1;        // half-finished ping-pong pair: colour whose newest pixels sit in planes_snap (capi_run.cu.inc)
     int wave_blocks = 0;   // acmmp_set_wave_emulation: resident blocks of the reference launch (0 = off)
+    int cold_left = 0;     // half-sweeps still counted as cold after a random initialisation (sweep_kernel<..., kPairMatrix>)
     int n = 0;   // images in the problem
     int W = 0, H = 0;
     std::vector<acmmp_camera> cams;

@@ -378,9 +378,17 @@ cudaError_t launch_sweep(const SweepLaunch &L, cudaStream_t st) {
     const size_t smem = sweep_smem_bytes(L.nsrc, boxes);
     // four CTAs per SM when their shared memory fits (1 KB per CTA is reserved by the system), else three
     const bool four = !boxes && 4 * (smem + 1024) <= (size_t)228 * 1024 && ACMMP_SWEEP_MAX_BLOCKS >= 4;
-    auto kernel = boxes ? sweep_kernel<true, true, 3>
-                        : (L.tex_u8 ? (four ? sweep_kernel<true, false, 4> : sweep_kernel<true, false, 3>)
-                                    : (four ? sweep_kernel<false, false, 4> : sweep_kernel<false, false, 3>));
+#ifdef ACMMP_PAIR_MATRIX_ALWAYS
+    const bool cold = true;
+#else
+    const bool cold = L.cold != 0;
+#endif
+    void (*kernel)(SweepArgs);
+    if (boxes) kernel = sweep_kernel<true, true, 3, false>;
+    else if (L.tex_u8) kernel = four ? (cold ? sweep_kernel<true, false, 4, true> : sweep_kernel<true, false, 4, false>)
+                                     : (cold ? sweep_kernel<true, false, 3, true> : sweep_kernel<true, false, 3, false>);
+    else kernel = four ? (cold ? sweep_kernel<false, false, 4, true> : sweep_kernel<false, false, 4, false>)
+                       : (cold ? sweep_kernel<false, false, 3, true> : sweep_kernel<false, false, 3, false>);
     // per-device attribute: see launch_init
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

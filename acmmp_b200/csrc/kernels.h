@@ -55,6 +55,7 @@ struct SweepLaunch {
     float sigma_spatial, sigma_color;
     int geom_consistency, planar_prior, hierarchy, compat;
     int wave_lo, wave_hi, ref_grid_x;   // wave emulation (sweep_kernel.cuh); wave_hi == 0: off
+    int cold;   // a half-sweep on a freshly randomised state: cost matrix by lane pairs (sweep_kernel<..., kPairMatrix>)
     unsigned long long *ncc_counter;   // nullable; 4096 slots
     // box staging (ncc.cuh): host copy of the tensor map over the R8 layers as linear bytes, or null; layer size
     const void *views_map;
