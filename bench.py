@@ -29,7 +29,7 @@ FLOP_PER_NCC = 1538.0          # 36 x 38 + 170
 # launches); ~1 % of what HBM could move in that time
 SWEEP_DRAM_BYTES_PER_LAUNCH = 432e6
 # the same for sweep_kernel<R8> (finest level, R8 unorm texels)
-SWEEP_DRAM_BYTES_PER_LAUNCH_U8 = 215e6   # profiles/r1o_sweep_u8_full_summary.txt: 148 MB read + 67 MB written
+SWEEP_DRAM_BYTES_PER_LAUNCH_U8 = 250e6   # profiles/r2ac_sweep_full_summary.txt (4 CTAs/SM): 160 MB read + 90 MB written (r1o, 3 CTAs: 148 + 67)
 HYP_PER_RUN = 29               # 1 (init) + 2 x 14; 30 for the hierarchy (upsample-init) run
 
 
