@@ -11,8 +11,17 @@
 //    its candidate strip, fetches the winning plane and scores it against all
 //    sources.  The 8 x (N-1) cost matrix lives in shared memory (the reference
 //    keeps it, plus six more 32-float arrays, in 1,888 B of per-thread local
-//    memory).  Votes, the multinomial view sampling and the arg-min / arg-max
-//    run on shuffles inside the group.
+//    memory).  Votes and the arg-min / arg-max run on shuffles inside the
+//    group, the multinomial view sampling on ballots (every lane replays the
+//    pixel's random stream; lane l owns the CDF entries of views l, l + 8, ...).
+//  * ONE inlined copy of the single-lane NCC loop serves the cost matrix
+//    (pass 0) and the refinement candidates (pass 1); the arms' planes, the
+//    pixel's plane, the candidates and the decision state are parked in shared
+//    memory around it (SweepGroupSmem), which is what lets four CTAs of 64
+//    registers share an SM.  Cold launches (right after a random
+//    initialisation) score the cost matrix by lane pairs instead
+//    (sweep_kernel<..., kPairMatrix>): a texture quad then holds two arm
+//    hypotheses instead of four.
 //  * the hypothesis-independent half of every NCC (36 bilateral weights and
 //    the reference-patch moments) is computed once per pixel per launch
 //    (RefPatch, ncc.cuh); camera-pair constants once per problem (PairConst).
@@ -20,8 +29,9 @@
 //    the views that were actually sampled (view weight > 0) - the reference
 //    scores all N-1 and multiplies the rest by zero - and those (candidate,
 //    view) tasks are spread over the 8 lanes.
-//  * the XORWOW state stays in registers for the whole sweep (every lane of a
-//    group carries an identical copy, so all lanes make the same draws).
+//  * the XORWOW state stays in registers from the first to the last draw of the
+//    pixel (every lane of a group carries an identical copy, so all lanes make
+//    the same draws).
 //  * same-colour reads (the V-shaped near-arm candidates sit on the colour
 //    being rewritten, a data race in the reference) see the state before the
 //    launch: planes / costs are ping-pong buffers (SweepArgs: read one, write
@@ -87,7 +97,7 @@ struct SweepArgs {
     // same-colour neighbours in blocks < wave_lo from the output buffers.
     int wave_lo, wave_hi, ref_grid_x;
     unsigned long long *ncc_counter;   // optional instrumentation: kNccCounterSlots slots, NCC evaluations issued
-    // sweep_kernel<true, true> only: the R8 layers as a pitch-linear (x, y, layer) byte tensor for TMA (box staging, ncc.cuh)
+    // sweep_kernel<true, true, ...> only: the R8 layers as a pitch-linear (x, y, layer) byte tensor for TMA (box staging, ncc.cuh)
     CUtensorMap views_map;
     int layer_w, layer_h;
 };
