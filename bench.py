@@ -880,6 +880,13 @@ def run_reference_kernels(args):
 
 
 def main():
+    # stdout carries the JSON line and nothing else: native libraries write to file descriptor 1 behind Python's back
+    # (NCCL prints "NCCL version ..." there when the box sets NCCL_DEBUG), so descriptor 1 is pointed at stderr and
+    # Python's own stdout keeps the original descriptor
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
