@@ -416,6 +416,10 @@ def run_ours(args):
                      "fp32": {"achieved": fp32_achieved, "peak": fp32_tflops, "unit": "TFLOP/s", "frac": fp32_achieved / fp32_tflops,
                               "mufu_gops_measured": mufu_gops},
                      "ncc_evals_per_step": {"init": ncc["init"], "sweeps": ncc["sweeps"], "reference_formulation": ncc_sweeps // args.steps},
+                     # not measured by this run: the binding units' utilisation of the same kernel under ncu --set full
+                     "ncu": {"source": "profiles/r2ae_sweep_full_summary.txt (one 1600x1200 R8 launch on converged state)",
+                             "l1tex_data_stage_busy": 0.856, "issue_slots_busy": 0.758, "t_stage_wavefronts_per_request": 1.22,
+                             "tex_l1_hit_rate": 0.96, "warps_active_of_peak": 0.468},
                      "note": "texture-pipe bound (ncu: l1tex data-stage is the top unit; HBM traffic is ~0.7 % of peak, no tensor-shaped work): "
                              "achieved = bilinear fetches issued by sweep_kernel (device-counted NCC evaluations x 36) / its time from CUDA events "
                              "on the launching stream, for the launches of the finest level (the dominant kernel; all_levels has the rest); "
