@@ -371,7 +371,10 @@ int acmmp_scan_set_texture_format(acmmp_scan *s, int format);
  * cp.async.bulk.tensor, placed where the tile's centre lands under its current plane; taps whose texels lie inside are
  * filtered from it with the texture unit's own 1/256 weights (bit-identical on 8-bit texels), every other tap goes
  * through the unit.  1 = on, 0 = off, -1 = the process default (environment ACMMP_BOX_STAGING, else the build's).
- * Results do not depend on the setting. */
+ * Results do not depend on the setting.
+ * (Another scheduling knob without an entry point: environment ACMMP_COLD_SWEEPS = number of half-sweeps after a random
+ * initialisation whose cost matrix is scored by lane pairs, default 2 on R8 levels and 3 on R32F ones - timing
+ * experiments only, results do not depend on it either: tests/test_gpu_cold_sweeps.py.) */
 int acmmp_set_box_staging(acmmp_ctx *ctx, int on);
 int acmmp_scan_set_box_staging(acmmp_scan *s, int on);
 int acmmp_scan_level_is_u8(const acmmp_scan *s);
